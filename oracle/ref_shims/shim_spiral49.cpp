@@ -1,0 +1,21 @@
+/* TEST INFRASTRUCTURE ONLY. Wraps the unmodified reference TU spiral/spiral49.cpp (compiled from
+ * /root/reference via -I, never copied) so tests can read its decision words and metrics. */
+#include "kvref.h"
+#include <stdlib.h>
+#include <stdio.h>
+#include <string.h>
+#include <memory.h>
+#include <limits.h>
+#include <assert.h>
+#include <stddef.h>
+#include <stdint.h>
+#include <immintrin.h>
+#include <pmmintrin.h>
+/* 'renormalize' is a non-static inline with a different body in every spiral TU (ODR hazard when all are
+ * linked into one library): give each TU its own name. */
+#define renormalize renormalize_spiral49
+#include "spiral/spiral49.cpp"
+#include "shim_c_style.h"
+KVREF_DEFINE_C_STYLE(spiral49, spiral49, 9, 4, 1,
+    create_spiral49, init_spiral49, update_spiral49, chainback_spiral49, delete_spiral49,
+    (void*)vp->old_metrics)
