@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""bench.py -- decoded Mbit/s (update + chainback) of the batched Viterbi decoder on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--codec ka9q27] ...
+
+One "step" = init + update + chainback of one batch of frames (BASELINE.json configs[1]: 1 Mi frames x
+2048 bits of K=7 r=1/2 per GPU; frames are independent, so ranks shard them with no collective: weak
+scaling). `value` is timed with inputs resident in HBM; `e2e` goes through b200v_batch_decode with host
+(pinned) buffers, copies included. Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "decoded Mbit/s (update+chainback)"
+UNIT = "Mbit/s"
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--codec", default="ka9q27")
+    p.add_argument("--frames", type=int, default=0, help="frames per GPU (default: 1 Mi for K<=9, 8192 for K=15)")
+    p.add_argument("--frame-bits", type=int, default=2048)
+    p.add_argument("--sigma", type=float, default=0.7, help="channel noise (0 = main.cpp's noiseless symbols)")
+    p.add_argument("--variant", type=int, default=0, help="kernel family: 0 auto, 1 generic, 2 specialised")
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--cpu-seconds", type=float, default=6.0)
+    return p.parse_args()
+
+
+# oracle registry name (CPU reference arm) for each product codec
+REF_NAME = {"ka9q27": "ka9q27", "ka9q29": "ka9q29", "ka9q615": "ka9q615", "spiral27": "spiral27",
+            "spiral29": "spiral29", "spiral47": "spiral47", "spiral49": "spiral49", "spiral615": "spiral615"}
+
+
+def codec_shape(codec):
+    import ka9q_viterbi_comparison_b200 as kv
+    k, r = C.c_int(), C.c_int()
+    kv.load_library().b200v_codec_shape(kv.CODEC_BY_NAME[codec], C.byref(k), C.byref(r))
+    return k.value, r.value
+
+
+def default_frames(K):
+    return 1 << 20 if K <= 9 else 8192
+
+
+def channel_params(lo, hi, sigma):
+    """Q8 fixed-point channel constants (run_snr_ber.cpp:317-365 shape): amp = mag/sqrt(1+sigma^2)."""
+    mag = (hi - lo) / 2.0
+    amp = mag / (1.0 + sigma * sigma) ** 0.5 if sigma > 0 else mag
+    return int(round(amp * 256)), int(round(amp * sigma * 256)), int(round(256 * (hi + lo) / 2.0)), lo, hi
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks sampling during the timed region
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.samples, self.stop_flag, self.thread = index, [], False, None
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.samples.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def start(self):
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join(timeout=6)
+        sm, mx, reasons = [], 0.0, set()
+        for s in self.samples:
+            if len(s) < 6:
+                continue
+            try:
+                sm.append(float(s[0]))
+                mx = max(mx, float(s[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU reference arm: the reference's own decoder on the host cores (oracle/_ref, else the oracle port)
+# ---------------------------------------------------------------------------------------------------
+def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None):
+    """Decode frames of `frame_bits` with one decoder instance per host thread for ~`seconds`.
+    Returns (Mbit/s aggregate, threads, kind, sample description)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as o
+    name = REF_NAME[codec]
+    c = o.codec_by_name(name)
+    nbytes = frame_bits // 8
+    T = frame_bits + c.K - 1
+    kind = "reference" if o.ref_available() else "port"
+    n_threads = n_threads or (os.cpu_count() or 1)
+    pool = [o.make_frame(c, nbytes, sigma, seed=0xB200, frame=f)[1] for f in range(16)]
+    # create serially: the reference's create_* fills process-global tables unguarded
+    decs = [(o.Ref(name, T) if kind == "reference" else o.Oracle(c, T)) for _ in range(n_threads)]
+    counts = [0] * n_threads
+    deadline = [0.0]
+
+    def work(i):
+        d = decs[i]
+        n = 0
+        while time.perf_counter() < deadline[0]:
+            for s in pool:
+                d.init(0)
+                d.update(s, T)
+                d.chainback(frame_bits)
+                n += 1
+        counts[i] = n
+
+    t0 = time.perf_counter()
+    deadline[0] = t0 + seconds
+    th = [threading.Thread(target=work, args=(i,)) for i in range(n_threads)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    dt = time.perf_counter() - t0
+    for d in decs:
+        d.close()
+    frames = sum(counts)
+    return frames * frame_bits / dt / 1e6, n_threads, kind, \
+        f"{frames} frames x {frame_bits} bits of {name}, sigma={sigma}, {n_threads} threads, {dt:.1f} s"
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    K, R = codec_shape(args.codec)
+    per_step = max(1.0, min(args.cpu_seconds, 240.0 / max(1, args.steps + args.warmup)))
+    vals = []
+    info = None
+    for i in range(args.warmup + args.steps):
+        v, cores, kind, sample = cpu_reference_rate(args.codec, args.frame_bits, args.sigma, per_step)
+        if i >= args.warmup:
+            vals.append(v)
+            info = (cores, kind, sample)
+    value = float(np.mean(vals))
+    frames = args.frames or default_frames(K)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"{args.codec} K={K} r=1/{R}: {frames} frames x {args.frame_bits} bits per GPU",
+                   "sigma": args.sigma},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": info[0], "kind": info[1], "sample": info[2]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------------
+def run_b200_arm(args):
+    import torch
+    import ka9q_viterbi_comparison_b200 as kv
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+
+    codec = kv.CODEC_BY_NAME[args.codec]
+    K, R = codec_shape(args.codec)
+    S = 1 << (K - 1)
+    nbits = args.frame_bits
+    T = nbits + K - 1
+    frames = args.frames or default_frames(K)
+    sym_bytes = kv.load_library().b200v_codec_symbol_bytes(codec)
+    lo, hi = {1: (0, 255)}.get(sym_bytes, (-127, 127))
+    srow, orow = T * R * sym_bytes, nbits // 8
+
+    dec = kv.BatchDecoder(codec, T, frames, device=local)
+    if args.variant:
+        dec.set_variant(args.variant)
+    stream = torch.cuda.current_stream()
+    dec.set_stream(stream.cuda_stream)
+
+    d_syms = torch.empty(frames * srow, dtype=torch.uint8, device=dev)
+    d_data = torch.empty(frames * orow, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(frames * orow, dtype=torch.uint8, device=dev)
+    amp_q8, sigma_q8, mean_q8, lo, hi = channel_params(lo, hi, args.sigma)
+    dec.generate_dev(d_syms, srow, d_data, orow, nbits, 0xB200, rank * frames, amp_q8, sigma_q8, mean_q8, lo, hi)
+    torch.cuda.synchronize()
+
+    def step():
+        dec.reset()
+        dec.update_dev(d_syms, srow, T)
+        dec.chainback_dev(d_out, orow, nbits)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    launches0 = dec.launch_count
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    upd_ms, cb_ms = [], []
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    total_ms = e0.elapsed_time(e1)
+    launches = dec.launch_count - launches0
+    # per-kernel device time (CUDA events on the launching stream, recorded inside the library)
+    for _ in range(3):
+        step()
+        u, c = dec.last_kernel_ms()
+        upd_ms.append(u)
+        cb_ms.append(c)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # correctness guard inside the bench: decoded output vs generated data
+    ber = float((torch.bitwise_xor(d_out, d_data).to(torch.int32).cpu().numpy().astype(np.uint8)
+                 [: 4096 * orow]).view(np.uint8).astype(np.uint8).__array__().tobytes().count(b"\x00") == 0)
+    err_bits = int(np.unpackbits(torch.bitwise_xor(d_out[: 4096 * orow], d_data[: 4096 * orow]).cpu().numpy()).sum())
+    ber = err_bits / float(4096 * nbits)
+
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    value = world * frames * nbits / (ms_per_step * 1e-3) / 1e6
+
+    # ---- end-to-end through the C-ABI batch entry point with host buffers ----
+    e2e = None
+    if not args.no_e2e:
+        lib = kv.load_library()
+        h_syms = lib.b200v_host_alloc_pinned(frames * srow)
+        h_out = lib.b200v_host_alloc_pinned(frames * orow)
+        if not h_syms or not h_out:
+            raise RuntimeError("pinned allocation failed")
+        lib.b200v_memcpy_d2h(local, h_syms, d_syms.data_ptr(), frames * srow)
+        e2e_steps = max(1, min(args.steps, 3))
+        for _ in range(1):
+            rc = lib.b200v_batch_decode(dec.h, h_syms, h_out, nbits)
+            assert rc == 0, lib.b200v_last_error()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            rc = lib.b200v_batch_decode(dec.h, h_syms, h_out, nbits)
+            assert rc == 0, lib.b200v_last_error()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": world * frames * nbits * e2e_steps / dt / 1e6, "unit": UNIT,
+               "h2d_bytes_per_step": frames * srow, "d2h_bytes_per_step": frames * orow, "steps": e2e_steps}
+        lib.b200v_host_free_pinned(h_syms)
+        lib.b200v_host_free_pinned(h_out)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (update): algorithmic bytes = symbols in + decision bits out ----
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    upd = float(np.median(upd_ms))
+    cb = float(np.median(cb_ms))
+    bytes_per_step_frame = R * sym_bytes + S / 8.0
+    achieved = frames * T * bytes_per_step_frame / (upd * 1e-3) / 1e9
+    lane_ops = frames * T * 4.0 * S                      # 4*S integer lane-ops per step
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+                "traffic": None, "kernel": "update", "kernel_ms": upd, "chainback_ms": cb,
+                "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "note": "4*S integer lane-ops per trellis step"}}
+
+    cpu = None
+    if not args.no_cpu_baseline and args.codec in REF_NAME:
+        v, cores, kind, sample = cpu_reference_rate(args.codec, nbits, args.sigma, args.cpu_seconds)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8" if sym_bytes == 1 else "u16", "data": "synthetic",
+        "config": {"workload": f"{args.codec} K={K} r=1/{R}: {frames} frames x {nbits} bits per GPU",
+                   "sigma": args.sigma, "kernel_variant": dec.variant, "l2": "inputs larger than L2"
+                   if frames * srow > 126e6 else "inputs smaller than L2", "sample_ber": ber},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,176 @@
+/* b200_viterbi.h -- C-ABI of libb200viterbi.so: batched Viterbi update + chainback on one B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the reference's decode hot path. The reference calls its decoders
+ * through five free functions per codec, wrapped by the adapter templates in
+ *   /root/reference/src/ka9q_interface.h:12-56   (create/init/update_blk/chainback/delete _viterbiXX_sse2)
+ *   /root/reference/src/spiral_interface.h:12-56 (create/init/update/chainback/delete _spiralXX)
+ * and the williamyang decoders through
+ *   /root/reference/src/main.cpp:163-187         (ViterbiDecoder_Core::reset / decoder_t::update / chainback).
+ * Every entry point below cites the reference function whose role it takes. The same five calls exist
+ * here on a *batch* of independent frames (b200v_batch_*); the per-codec single-frame names of the
+ * reference are provided on top of it by include/ref_compat/ (C++ linkage, as in the reference).
+ *
+ * Plain pointers and sizes only. Functions return 0 on success and a negative b200v_status on failure;
+ * b200v_last_error() gives the message of the calling thread's last failure. There is no CPU fallback:
+ * without a CUDA device every compute entry point fails with B200V_ERR_CUDA.
+ */
+#ifndef B200_VITERBI_H
+#define B200_VITERBI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200V_VERSION 1
+#define B200V_MAX_R 8
+
+typedef enum b200v_status {
+    B200V_OK = 0,
+    B200V_ERR_ARG = -1,      /* bad argument (unknown codec, K/R mismatch, sizes out of range) */
+    B200V_ERR_CUDA = -2,     /* CUDA runtime failure (no device, launch error, ...) */
+    B200V_ERR_NOMEM = -3,    /* device or host allocation failed */
+    B200V_ERR_STATE = -4     /* call sequence error (e.g. update past the allocated length) */
+} b200v_status;
+
+/* Arithmetic policy + code: which reference decoder's metric width, saturation, renormalisation and
+ * tie-break are reproduced bit for bit. */
+typedef enum b200v_codec {
+    B200V_KA9Q27 = 0,     /* ka9q_libfec_port/viterbi27_sse2.cpp   K=7  r=1/2 u8 modular            */
+    B200V_KA9Q29 = 1,     /* ka9q_libfec_port/viterbi29_sse2.cpp   K=9  r=1/2 u8 modular            */
+    B200V_KA9Q615 = 2,    /* ka9q_libfec_port/viterbi615_sse2.cpp  K=15 r=1/6 s16 saturating        */
+    B200V_KA9Q224 = 3,    /* ka9q_libfec_port/viterbi224_sse2.cpp  K=24 r=1/2 s16 saturating        */
+    B200V_SPIRAL27 = 4,   /* spiral/spiral27.cpp                   K=7  r=1/2 u8 saturating         */
+    B200V_SPIRAL29 = 5,   /* spiral/spiral29.cpp                   K=9  r=1/2                       */
+    B200V_SPIRAL47 = 6,   /* spiral/spiral47.cpp                   K=7  r=1/4                       */
+    B200V_SPIRAL49 = 7,   /* spiral/spiral49.cpp                   K=9  r=1/4                       */
+    B200V_SPIRAL615 = 8,  /* spiral/spiral615.cpp                  K=15 r=1/6                       */
+    B200V_WY_U8 = 9,      /* viterbi/x86/viterbi_decoder_{sse,avx}_u8.h   any K,R; int8 symbols      */
+    B200V_WY_U16 = 10     /* viterbi/x86/viterbi_decoder_{sse,avx}_u16.h  any K,R; int16 symbols     */
+} b200v_codec;
+
+/* Numeric configuration of the williamyang decoders: ViterbiDecoder_Config<error_t>
+ * (viterbi/viterbi_decoder_config.h:12-17) plus the branch-table symbol values
+ * (viterbi/viterbi_branch_table.h:34-36). NULL in b200v_batch_create selects main.cpp's defaults
+ * (src/viterbi_configs.h:22-50: soft8 for WY_U8, soft16 for WY_U16). Ignored by ka9q/spiral codecs. */
+typedef struct b200v_wy_config {
+    int soft_decision_high, soft_decision_low;
+    unsigned soft_decision_max_error;
+    unsigned initial_start_error;
+    unsigned initial_non_start_error;
+    unsigned renormalisation_threshold;
+} b200v_wy_config;
+
+typedef struct b200v_batch b200v_batch;   /* opaque, like the reference's struct v27 / spiral27 */
+
+/* ---- library ---- */
+int b200v_version(void);
+const char* b200v_last_error(void);
+int b200v_device_count(void);
+/* K and R of a fixed codec (0,0 for the WY_* families). */
+int b200v_codec_shape(int codec, int* K, int* R);
+/* Bytes per input symbol (1, or 2 for WY_U16) and per path metric (1 or 2). */
+int b200v_codec_symbol_bytes(int codec);
+int b200v_codec_metric_bytes(int codec);
+
+/* ---- instance lifetime ----
+ * Takes the role of create_viterbiXX_sse2(poly,len) (viterbi27_sse2.cpp:57-75), create_spiralXX
+ * (spiral27.cpp:62-78) and of ViterbiBranchTable + ViterbiDecoder_Core construction (main.cpp:163-165),
+ * for n_frames independent frames at once.
+ *   K,R          must match the codec (or be 0) for ka9q/spiral; required for WY_*
+ *   poly[R]      generator polynomials, LSB = newest input bit; spiral codecs accept a negative value as
+ *                "inverted output" (spiral27.cpp:69). Unlike the reference (process-global table filled by
+ *                the first create), the table is per instance.
+ *   frame_steps  trellis steps per frame incl. the K-1 tail steps (= `len` as main.cpp:247 passes it)
+ *   device       CUDA device ordinal
+ * Returns NULL on failure (see b200v_last_error). The instance is initialised as by init(.., 0). */
+b200v_batch* b200v_batch_create(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
+                                int device, const b200v_wy_config* wy_config);
+/* delete_viterbiXX_sse2 (viterbi27_sse2.cpp:108-115). NULL is accepted. */
+void b200v_batch_destroy(b200v_batch* h);
+
+/* Run the instance's work on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL restores the
+ * instance's own stream. */
+int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream);
+/* Choose the kernel family: 0 = automatic (fastest available for the codec/polynomials),
+ * 1 = generic shared-memory kernel (any K<=16, any polynomial), 2 = register-resident specialised kernel.
+ * Returns B200V_ERR_ARG if the requested family does not exist for this instance. */
+int b200v_batch_set_variant(b200v_batch* h, int variant);
+int b200v_batch_get_variant(const b200v_batch* h);
+
+/* init_viterbiXX_sse2(p, starting_state) (viterbi27_sse2.cpp:42-54), init_spiralXX (spiral27.cpp:53-59),
+ * ViterbiDecoder_Core::reset (viterbi_decoder_core.h:202-211): all frames. Asynchronous on the stream. */
+int b200v_batch_init(b200v_batch* h, int starting_state);
+
+/* update_viterbiXX_blk_sse2(p, syms, nbits) (viterbi27_sse2.cpp:119-175 ...), update_spiralXX
+ * (spiral27.cpp:383-386), decoder_t::update (sse_u8.h:45-70). `nsteps` trellis steps for every frame.
+ * ka9q/WY codecs continue from the previous call's position (streaming); spiral codecs restart at step 0
+ * and drop an odd trailing step, exactly as the reference does.
+ *   _dev : syms is a device pointer; frame f's symbols start at syms + f*frame_stride_bytes and hold
+ *          nsteps*R symbols (u8, int8 or int16 per codec). Asynchronous on the stream.
+ *   host : syms is a host pointer with the same layout; copies in, runs, and returns after completion
+ *          (the reference's callers time each call on the host, main.cpp:264-278). */
+int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t frame_stride_bytes, int nsteps);
+int b200v_batch_update(b200v_batch* h, const void* syms, size_t frame_stride_bytes, int nsteps);
+
+/* chainback_viterbiXX_sse2(p, data, nbits, endstate) (viterbi27_sse2.cpp:78-105, viterbi615_sse2.cpp:65-91,
+ * viterbi224_sse2.cpp:79-121 -- reproduced literally), chainback_spiralXX (spiral27.cpp:81-120),
+ * ViterbiDecoder_Core::chainback (viterbi_decoder_core.h:214-236). Frame f's (nbits+7)/8 output bytes go
+ * to data + f*frame_stride_bytes. Decoded bit n lands in byte n/8, bit 7-(n%8). */
+int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t frame_stride_bytes, unsigned nbits,
+                              unsigned endstate);
+int b200v_batch_chainback(b200v_batch* h, uint8_t* data, size_t frame_stride_bytes, unsigned nbits,
+                          unsigned endstate);
+/* Per-frame return value of the reference's chainback: the end-state path metric for KA9Q615
+ * (viterbi615_sse2.cpp:76,90), 0 otherwise. Valid after a chainback; copies n_frames ints to the host. */
+int b200v_batch_chainback_results(b200v_batch* h, int* results);
+
+/* Batch entry point (new): init + update(frame_steps) + chainback(nbits) for all frames from
+ * host buffers, host<->device copies included and overlapped with compute in chunks of frames.
+ * syms: [n_frames][frame_steps*R] symbols, data: [n_frames][(nbits+7)/8] bytes, both densely packed. */
+int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits);
+
+/* Wait for everything queued on the instance's stream. */
+int b200v_batch_sync(b200v_batch* h);
+
+/* ---- introspection (parity tests, SURVEY 8b "b200v_batch_get_decisions") ---- */
+/* Canonical decision vectors of one frame: S/8 bytes per step, bit n of the little-endian vector is the
+ * decision of new state n (the layout every reference decoder uses). Host output buffer. */
+int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, int nsteps, uint8_t* out);
+/* Current path metrics of one frame: S elements of b200v_codec_metric_bytes() each. Host buffer. */
+int b200v_batch_get_metrics(b200v_batch* h, int frame, void* out);
+/* Trellis steps consumed since the last init (the reference's dp / m_current_decoded_bit cursor). */
+int b200v_batch_steps_done(const b200v_batch* h);
+
+/* Device time of the most recent update / chainback launches on this instance, measured with CUDA events
+ * on the launching stream (ms). Synchronises the stream. Either pointer may be NULL. */
+int b200v_batch_last_kernel_ms(b200v_batch* h, float* update_ms, float* chainback_ms);
+/* Number of kernels this instance has launched since creation. */
+long long b200v_batch_launch_count(const b200v_batch* h);
+
+/* ---- synthetic input on the device (encoder + integer AWGN channel + quantiser) ----
+ * Fills frame f (global index frame0+f) of d_syms with the encoded, noisy, quantised symbols of
+ * pseudo-random data derived from `seed`, and optionally the data bytes themselves into d_data
+ * ((nbits)/8 bytes per frame, may be NULL). Restates src/util.h:15-62 +
+ * convolutional_encoder_shift_register.h:42-62 with an integer-only channel so that host and device
+ * generators agree bit for bit. amp_q8 / sigma_q8 / mean_q8 are Q8 fixed-point channel constants,
+ * lo/hi the clamp range (0/255, +-3, +-127). Asynchronous on the instance's stream. */
+int b200v_batch_generate_dev(b200v_batch* h, void* d_syms, size_t sym_frame_stride_bytes,
+                             uint8_t* d_data, size_t data_frame_stride_bytes,
+                             unsigned nbits, uint64_t seed, uint64_t frame0,
+                             int amp_q8, int sigma_q8, int mean_q8, int lo, int hi);
+
+/* ---- device / pinned-host memory helpers (so a C host needs nothing but this library) ---- */
+void* b200v_device_alloc(int device, size_t bytes);
+void  b200v_device_free(int device, void* p);
+void* b200v_host_alloc_pinned(size_t bytes);
+void  b200v_host_free_pinned(void* p);
+int   b200v_memcpy_h2d(int device, void* dst, const void* src, size_t bytes);
+int   b200v_memcpy_d2h(int device, void* dst, const void* src, size_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_VITERBI_H */

@@ -1,0 +1,490 @@
+// api.cu -- the C-ABI of include/b200_viterbi.h: instance state, buffer management, kernel dispatch.
+// Host code only; every compute call ends in a kernel launch from acs_*.cu / chainback.cu (no CPU path).
+#include "../../include/b200_viterbi.h"
+#include "kernels.h"
+#include "decision_layout.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace b200v;
+
+// ---------------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CUDA_TRY(expr)                                                                                   \
+    do {                                                                                                 \
+        cudaError_t e_ = (expr);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(e_ == cudaErrorMemoryAllocation ? B200V_ERR_NOMEM : B200V_ERR_CUDA,              \
+                        "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__);    \
+    } while (0)
+
+extern "C" const char* b200v_last_error(void) { return g_err; }
+extern "C" int b200v_version(void) { return B200V_VERSION; }
+extern "C" int b200v_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// codec table
+// ---------------------------------------------------------------------------------------------------
+struct CodecInfo { int policy, K, R; };
+static bool codec_info(int codec, CodecInfo& ci) {
+    switch (codec) {
+    case B200V_KA9Q27: ci = { P_KA9Q_U8_MOD, 7, 2 }; return true;
+    case B200V_KA9Q29: ci = { P_KA9Q_U8_MOD, 9, 2 }; return true;
+    case B200V_KA9Q615: ci = { P_KA9Q_S16_615, 15, 6 }; return true;
+    case B200V_KA9Q224: ci = { P_KA9Q_S16_224, 24, 2 }; return true;
+    case B200V_SPIRAL27: ci = { P_SPIRAL_R2, 7, 2 }; return true;
+    case B200V_SPIRAL29: ci = { P_SPIRAL_R2, 9, 2 }; return true;
+    case B200V_SPIRAL47: ci = { P_SPIRAL_R4, 7, 4 }; return true;
+    case B200V_SPIRAL49: ci = { P_SPIRAL_R4, 9, 4 }; return true;
+    case B200V_SPIRAL615: ci = { P_SPIRAL_615, 15, 6 }; return true;
+    case B200V_WY_U8: ci = { P_WY_U8, 0, 0 }; return true;
+    case B200V_WY_U16: ci = { P_WY_U16, 0, 0 }; return true;
+    default: return false;
+    }
+}
+
+extern "C" int b200v_codec_shape(int codec, int* K, int* R) {
+    CodecInfo ci;
+    if (!codec_info(codec, ci)) return fail(B200V_ERR_ARG, "unknown codec %d", codec);
+    if (K) *K = ci.K;
+    if (R) *R = ci.R;
+    return B200V_OK;
+}
+extern "C" int b200v_codec_symbol_bytes(int codec) { return codec == B200V_WY_U16 ? 2 : 1; }
+extern "C" int b200v_codec_metric_bytes(int codec) {
+    return (codec == B200V_KA9Q615 || codec == B200V_KA9Q224 || codec == B200V_WY_U16) ? 2 : 1;
+}
+
+// Policy constants; each cites where the reference fixes the value.
+static int fill_params(CodecParams& c, int codec, int K, int R, const int* poly, const b200v_wy_config* wy) {
+    CodecInfo ci;
+    if (!codec_info(codec, ci)) return fail(B200V_ERR_ARG, "unknown codec %d", codec);
+    if (ci.K) {
+        if ((K && K != ci.K) || (R && R != ci.R))
+            return fail(B200V_ERR_ARG, "codec %d is K=%d R=%d, got K=%d R=%d", codec, ci.K, ci.R, K, R);
+        K = ci.K; R = ci.R;
+    }
+    if (K < 3 || K > 24) return fail(B200V_ERR_ARG, "constraint length K=%d out of range [3,24]", K);
+    if (R < 2 || R > MAX_R) return fail(B200V_ERR_ARG, "code rate 1/%d out of range [2,%d]", R, MAX_R);
+    if (!poly) return fail(B200V_ERR_ARG, "poly is NULL");
+    memset(&c, 0, sizeof(c));
+    c.policy = ci.policy; c.K = K; c.R = R; c.S = 1 << (K - 1);
+    for (int i = 0; i < R; i++) c.poly[i] = poly[i];
+    c.sym_bytes = b200v_codec_symbol_bytes(codec);
+    c.metric_bytes = b200v_codec_metric_bytes(codec);
+    c.soft_hi = 255; c.soft_lo = 0;
+    switch (ci.policy) {
+    case P_KA9Q_U8_MOD:   // viterbi27_sse2.cpp:46-52
+        c.init_other = 63; c.init_start = 0; c.max_error = 15; break;
+    case P_KA9Q_S16_615:  // viterbi615_sse2.cpp:33-39, :160
+        c.init_other = -32768 + 1000; c.init_start = -32768; c.max_error = 255 * R;
+        c.renorm_threshold = 32767 - 12750; break;
+    case P_KA9Q_S16_224:  // viterbi224_sse2.cpp:39-45, :226
+        c.init_other = -32768 + 5000; c.init_start = -32768; c.max_error = 510; c.renorm_threshold = 25000; break;
+    case P_SPIRAL_R2:     // spiral27.cpp:54-57, :236; spiral29.cpp:507
+        c.init_other = 63; c.max_error = 63; c.renorm_threshold = 210; break;
+    case P_SPIRAL_R4:     // spiral47.cpp:313; spiral49.cpp:790
+        c.init_other = 63; c.max_error = 63; c.renorm_threshold = (K == 9) ? 103 : 126; break;
+    case P_SPIRAL_615:    // spiral615.cpp:240, :269
+        c.init_other = 63; c.max_error = 94; c.renorm_threshold = 74; break;
+    case P_WY_U8:         // src/viterbi_configs.h:37-50 (soft8)
+        c.soft_hi = 3; c.soft_lo = -3; c.max_error = (6 * R) & 0xff; c.init_other = (12 * R) & 0xff;
+        c.renorm_threshold = 255 - ((12 * R) & 0xff); break;
+    case P_WY_U16:        // src/viterbi_configs.h:22-35 (soft16)
+        c.soft_hi = 127; c.soft_lo = -127; c.max_error = 254 * R; c.init_other = 1270 * R;
+        c.renorm_threshold = 65535 - 1270 * R; break;
+    }
+    if (wy && policy_is_wy(ci.policy)) {
+        c.soft_hi = wy->soft_decision_high; c.soft_lo = wy->soft_decision_low;
+        c.max_error = (int)wy->soft_decision_max_error;
+        c.init_start = (int)wy->initial_start_error;
+        c.init_other = (int)wy->initial_non_start_error;
+        c.renorm_threshold = (int)wy->renormalisation_threshold;
+    }
+    return B200V_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// instance
+// ---------------------------------------------------------------------------------------------------
+struct b200v_batch {
+    int codec = 0;
+    CodecParams c{};
+    int n_frames = 0, frame_steps = 0, dec_rows = 0, row_words = 0;
+    int device = 0;
+    int cursor = 0;              // trellis steps consumed since init
+    int variant = 1;             // kernel family in use (1 generic, 2 register-resident)
+    int layout = DL_BALLOT_FRAME_MAJOR;
+    bool has_fast = false;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev_u0 = nullptr, ev_u1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
+    bool timed_update = false, timed_chainback = false;
+    long long launches = 0;
+    // device buffers
+    void* d_dec = nullptr;       size_t dec_bytes = 0;
+    uint16_t* d_metrics = nullptr;
+    uint8_t* d_cw = nullptr;
+    int* d_results = nullptr;
+    // lazily allocated staging for the host-pointer entry points
+    void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
+    uint8_t* d_out_stage = nullptr; size_t out_stage_bytes = 0;
+};
+
+static void free_all(b200v_batch* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_cw); cudaFree(h->d_results);
+    cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
+    if (h->ev_u0) cudaEventDestroy(h->ev_u0);
+    if (h->ev_u1) cudaEventDestroy(h->ev_u1);
+    if (h->ev_c0) cudaEventDestroy(h->ev_c0);
+    if (h->ev_c1) cudaEventDestroy(h->ev_c1);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+}
+
+static int popcount32(uint32_t x) { return __builtin_popcount(x); }
+
+static int create_impl(b200v_batch* h, int starting_state);
+
+extern "C" b200v_batch* b200v_batch_create(int codec, int K, int R, const int* poly, int frame_steps,
+                                           int n_frames, int device, const b200v_wy_config* wy_config) {
+    CodecParams c;
+    if (fill_params(c, codec, K, R, poly, wy_config) != B200V_OK) return nullptr;
+    if (frame_steps <= 0 || n_frames <= 0) {
+        fail(B200V_ERR_ARG, "frame_steps=%d n_frames=%d must be positive", frame_steps, n_frames);
+        return nullptr;
+    }
+    if (c.K > 16) {
+        fail(B200V_ERR_ARG, "K=%d: only K<=16 is implemented in this build (K=24 kernel family pending)", c.K);
+        return nullptr;
+    }
+    b200v_batch* h = new (std::nothrow) b200v_batch();
+    if (!h) { fail(B200V_ERR_NOMEM, "host allocation failed"); return nullptr; }
+    h->codec = codec; h->c = c; h->n_frames = n_frames; h->frame_steps = frame_steps; h->device = device;
+    if (create_impl(h, 0) != B200V_OK) { free_all(h); return nullptr; }
+    return h;
+}
+
+extern "C" void b200v_batch_destroy(b200v_batch* h) { free_all(h); }
+
+static int create_impl(b200v_batch* h, int starting_state) {
+    const CodecParams& c = h->c;
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
+    CUDA_TRY(cudaEventCreate(&h->ev_u0)); CUDA_TRY(cudaEventCreate(&h->ev_u1));
+    CUDA_TRY(cudaEventCreate(&h->ev_c0)); CUDA_TRY(cudaEventCreate(&h->ev_c1));
+
+    // the reference allocates len + K-1 decision rows (viterbi27_sse2.cpp:72)
+    h->dec_rows = h->frame_steps + c.K - 1;
+    h->row_words = c.S / 32 < 2 ? 2 : c.S / 32;
+    h->dec_bytes = (size_t)h->n_frames * h->dec_rows * h->row_words * sizeof(uint32_t);
+    CUDA_TRY(cudaMalloc(&h->d_dec, h->dec_bytes));
+    CUDA_TRY(cudaMalloc(&h->d_metrics, (size_t)h->n_frames * c.S * sizeof(uint16_t)));
+    CUDA_TRY(cudaMalloc(&h->d_results, (size_t)h->n_frames * sizeof(int)));
+    CUDA_TRY(cudaMemsetAsync(h->d_results, 0, (size_t)h->n_frames * sizeof(int), h->stream));
+
+    // code word of butterfly j: bit i = parity((2j) & poly_i) (viterbi27_sse2.cpp:61-70,
+    // viterbi_branch_table.h:44-54); spiral: a negative polynomial inverts the bit (spiral27.cpp:69)
+    const int H = c.S / 2;
+    std::vector<uint8_t> cw((size_t)H, 0);
+    for (int i = 0; i < c.R; i++) {
+        const int p = c.poly[i];
+        const bool inv = policy_is_spiral(c.policy) && p < 0;
+        const uint32_t ap = (uint32_t)(inv ? -p : p);
+        for (int j = 0; j < H; j++)
+            cw[j] |= (uint8_t)((((unsigned)popcount32((2u * (uint32_t)j) & ap) & 1u) ^ (inv ? 1u : 0u)) << i);
+    }
+    CUDA_TRY(cudaMalloc(&h->d_cw, (size_t)H));
+    CUDA_TRY(cudaMemcpyAsync(h->d_cw, cw.data(), (size_t)H, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));   // cw is a local vector
+
+    const GenericPlan plan = generic_plan(c);
+    if (plan.smem_bytes > 227 * 1024)
+        return fail(B200V_ERR_ARG, "K=%d needs %d bytes of shared memory per block", c.K, plan.smem_bytes);
+    h->variant = 1;
+    h->layout = DL_BALLOT_FRAME_MAJOR;
+    return b200v_batch_init(h, starting_state);
+}
+
+extern "C" int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->own_stream;
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (variant == 0) variant = h->has_fast ? 2 : 1;
+    if (variant == 1) { h->variant = 1; return B200V_OK; }
+    if (variant == 2 && h->has_fast) { h->variant = 2; return B200V_OK; }
+    return fail(B200V_ERR_ARG, "kernel family %d is not available for this instance", variant);
+}
+extern "C" int b200v_batch_get_variant(const b200v_batch* h) { return h ? h->variant : 0; }
+
+extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(launch_init_metrics(h->d_metrics, h->n_frames, h->c, starting_state, h->stream));
+    h->launches++;
+    h->cursor = 0;
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t frame_stride_bytes, int nsteps) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (nsteps < 0 || (!d_syms && nsteps > 0)) return fail(B200V_ERR_ARG, "bad symbol buffer / step count");
+    const CodecParams& c = h->c;
+    if (policy_is_spiral(c.policy)) {   // spiral27.cpp:383-386: restart at row 0, nbits/2 double-steps
+        h->cursor = 0;
+        nsteps = (nsteps / 2) * 2;
+    }
+    if (h->cursor + nsteps > h->dec_rows)
+        return fail(B200V_ERR_STATE, "update of %d steps at step %d exceeds the %d decision rows allocated",
+                    nsteps, h->cursor, h->dec_rows);
+    if (nsteps > 0 && frame_stride_bytes < (size_t)nsteps * c.R * c.sym_bytes && h->n_frames > 1)
+        return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
+    if (nsteps > 0) {
+        GenericArgs a{};
+        a.c = c; a.syms = d_syms; a.sym_stride = frame_stride_bytes; a.nsteps = nsteps; a.step0 = h->cursor;
+        a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
+        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames;
+        CUDA_TRY(launch_acs_generic(a, h->stream));
+        h->launches++;
+    }
+    CUDA_TRY(cudaEventRecord(h->ev_u1, h->stream));
+    h->timed_update = true;
+    h->cursor += nsteps;
+    return B200V_OK;
+}
+
+static int ensure_stage(void** p, size_t* have, size_t need) {
+    if (*have >= need) return B200V_OK;
+    if (*p) { CUDA_TRY(cudaFree(*p)); *p = nullptr; *have = 0; }
+    CUDA_TRY(cudaMalloc(p, need));
+    *have = need;
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_update(b200v_batch* h, const void* syms, size_t frame_stride_bytes, int nsteps) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (nsteps < 0 || (!syms && nsteps > 0)) return fail(B200V_ERR_ARG, "bad symbol buffer / step count");
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t row = (size_t)nsteps * h->c.R * h->c.sym_bytes;
+    if (h->n_frames == 1) frame_stride_bytes = row;
+    if (row > 0) {
+        int rc = ensure_stage(&h->d_syms_stage, &h->syms_stage_bytes, row * h->n_frames);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(h->d_syms_stage, row, syms, frame_stride_bytes, row, (size_t)h->n_frames,
+                                   cudaMemcpyHostToDevice, h->stream));
+    }
+    int rc = b200v_batch_update_dev(h, h->d_syms_stage, row, nsteps);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t frame_stride_bytes,
+                                         unsigned nbits, unsigned endstate) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (!d_data && nbits) return fail(B200V_ERR_ARG, "NULL output buffer");
+    const CodecParams& c = h->c;
+    const unsigned rows_needed = nbits + (c.policy == P_KA9Q_S16_224 ? 0u : (unsigned)(c.K - 1));
+    if (rows_needed > (unsigned)h->dec_rows)
+        return fail(B200V_ERR_STATE, "chainback of %u bits needs %u decision rows, %d allocated", nbits,
+                    rows_needed, h->dec_rows);
+    CUDA_TRY(cudaSetDevice(h->device));
+    ChainbackArgs a{};
+    a.c = c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
+    a.n_frames = h->n_frames; a.metrics = h->d_metrics; a.out = d_data; a.out_stride = frame_stride_bytes;
+    a.nbits = nbits; a.endstate = endstate; a.results = h->d_results;
+    CUDA_TRY(cudaEventRecord(h->ev_c0, h->stream));
+    CUDA_TRY(launch_chainback(a, h->stream));
+    h->launches++;
+    CUDA_TRY(cudaEventRecord(h->ev_c1, h->stream));
+    h->timed_chainback = true;
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_chainback(b200v_batch* h, uint8_t* data, size_t frame_stride_bytes, unsigned nbits,
+                                     unsigned endstate) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (!data && nbits) return fail(B200V_ERR_ARG, "NULL output buffer");
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t row = (nbits + 7) / 8;
+    if (h->n_frames == 1) frame_stride_bytes = row;
+    if (row == 0) return B200V_OK;
+    int rc = ensure_stage((void**)&h->d_out_stage, &h->out_stage_bytes, row * h->n_frames);
+    if (rc) return rc;
+    rc = b200v_batch_chainback_dev(h, h->d_out_stage, row, nbits, endstate);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpy2DAsync(data, frame_stride_bytes, h->d_out_stage, row, row, (size_t)h->n_frames,
+                               cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_chainback_results(b200v_batch* h, int* results) {
+    if (!h || !results) return fail(B200V_ERR_ARG, "NULL argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaMemcpyAsync(results, h->d_results, (size_t)h->n_frames * sizeof(int), cudaMemcpyDeviceToHost,
+                             h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    int rc = b200v_batch_init(h, 0);
+    if (rc) return rc;
+    const size_t srow = (size_t)h->frame_steps * h->c.R * h->c.sym_bytes;
+    rc = b200v_batch_update(h, syms, srow, h->frame_steps);
+    if (rc) return rc;
+    return b200v_batch_chainback(h, data, (nbits + 7) / 8, nbits, 0);
+}
+
+extern "C" int b200v_batch_sync(b200v_batch* h) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return B200V_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// introspection
+// ---------------------------------------------------------------------------------------------------
+extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, int nsteps, uint8_t* out) {
+    if (!h || !out) return fail(B200V_ERR_ARG, "NULL argument");
+    if (frame < 0 || frame >= h->n_frames || step0 < 0 || nsteps < 0 || step0 + nsteps > h->dec_rows)
+        return fail(B200V_ERR_ARG, "frame/step range out of bounds");
+    CUDA_TRY(cudaSetDevice(h->device));
+    const int S = h->c.S;
+    const size_t nb = (size_t)S / 8;
+    memset(out, 0, nb * nsteps);
+    if (h->layout == DL_BALLOT_FRAME_MAJOR) {
+        std::vector<uint32_t> rows((size_t)nsteps * h->row_words);
+        const uint32_t* src = (const uint32_t*)h->d_dec + ((size_t)frame * h->dec_rows + step0) * h->row_words;
+        CUDA_TRY(cudaMemcpyAsync(rows.data(), src, rows.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        for (int t = 0; t < nsteps; t++) {
+            const uint32_t* r = rows.data() + (size_t)t * h->row_words;
+            uint8_t* o = out + (size_t)t * nb;
+            for (int n = 0; n < S; n++) {
+                unsigned w, b;
+                ballot_position((unsigned)n, w, b);
+                o[n >> 3] |= (uint8_t)(((r[w] >> b) & 1u) << (n & 7));
+            }
+        }
+        return B200V_OK;
+    }
+    return fail(B200V_ERR_STATE, "unknown decision layout %d", h->layout);
+}
+
+extern "C" int b200v_batch_get_metrics(b200v_batch* h, int frame, void* out) {
+    if (!h || !out) return fail(B200V_ERR_ARG, "NULL argument");
+    if (frame < 0 || frame >= h->n_frames) return fail(B200V_ERR_ARG, "frame out of bounds");
+    CUDA_TRY(cudaSetDevice(h->device));
+    const int S = h->c.S;
+    std::vector<uint16_t> m((size_t)S);
+    CUDA_TRY(cudaMemcpyAsync(m.data(), h->d_metrics + (size_t)frame * S, (size_t)S * 2, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (h->c.metric_bytes == 2) memcpy(out, m.data(), (size_t)S * 2);
+    else for (int i = 0; i < S; i++) ((uint8_t*)out)[i] = (uint8_t)m[i];
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_steps_done(const b200v_batch* h) { return h ? h->cursor : 0; }
+
+extern "C" int b200v_batch_last_kernel_ms(b200v_batch* h, float* update_ms, float* chainback_ms) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (update_ms) {
+        *update_ms = 0.f;
+        if (h->timed_update) CUDA_TRY(cudaEventElapsedTime(update_ms, h->ev_u0, h->ev_u1));
+    }
+    if (chainback_ms) {
+        *chainback_ms = 0.f;
+        if (h->timed_chainback) CUDA_TRY(cudaEventElapsedTime(chainback_ms, h->ev_c0, h->ev_c1));
+    }
+    return B200V_OK;
+}
+
+extern "C" long long b200v_batch_launch_count(const b200v_batch* h) { return h ? h->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------------
+// synthetic input
+// ---------------------------------------------------------------------------------------------------
+extern "C" int b200v_batch_generate_dev(b200v_batch* h, void* d_syms, size_t sym_frame_stride_bytes,
+                                        uint8_t* d_data, size_t data_frame_stride_bytes, unsigned nbits,
+                                        uint64_t seed, uint64_t frame0, int amp_q8, int sigma_q8, int mean_q8,
+                                        int lo, int hi) {
+    if (!h || !d_syms) return fail(B200V_ERR_ARG, "NULL argument");
+    if (nbits % 8) return fail(B200V_ERR_ARG, "nbits=%u must be a multiple of 8", nbits);
+    CUDA_TRY(cudaSetDevice(h->device));
+    GenerateArgs a{};
+    a.c = h->c; a.syms = d_syms; a.sym_stride = sym_frame_stride_bytes; a.data = d_data;
+    a.data_stride = data_frame_stride_bytes; a.nbits = nbits; a.seed = seed; a.frame0 = frame0;
+    a.amp_q8 = amp_q8; a.sigma_q8 = sigma_q8; a.mean_q8 = mean_q8; a.lo = lo; a.hi = hi; a.n_frames = h->n_frames;
+    CUDA_TRY(launch_generate(a, h->stream));
+    h->launches++;
+    return B200V_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// memory helpers
+// ---------------------------------------------------------------------------------------------------
+extern "C" void* b200v_device_alloc(int device, size_t bytes) {
+    void* p = nullptr;
+    if (cudaSetDevice(device) != cudaSuccess || cudaMalloc(&p, bytes) != cudaSuccess) {
+        fail(B200V_ERR_NOMEM, "cudaMalloc(%zu) on device %d failed: %s", bytes, device,
+             cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+extern "C" void b200v_device_free(int device, void* p) {
+    if (p && cudaSetDevice(device) == cudaSuccess) cudaFree(p);
+}
+extern "C" void* b200v_host_alloc_pinned(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+        fail(B200V_ERR_NOMEM, "cudaMallocHost(%zu) failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+extern "C" void b200v_host_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+extern "C" int b200v_memcpy_h2d(int device, void* dst, const void* src, size_t bytes) {
+    CUDA_TRY(cudaSetDevice(device));
+    CUDA_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+    return B200V_OK;
+}
+extern "C" int b200v_memcpy_d2h(int device, void* dst, const void* src, size_t bytes) {
+    CUDA_TRY(cudaSetDevice(device));
+    CUDA_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+    return B200V_OK;
+}

@@ -1,0 +1,68 @@
+// chainback.cu -- traceback kernels: sequential within a frame, parallel across frames (one thread per
+// frame). Takes the role of chainback_viterbiXX_sse2 (viterbi27_sse2.cpp:78-105, viterbi615_sse2.cpp:65-91),
+// chainback_spiralXX (spiral27.cpp:81-120) and ViterbiDecoder_Core::chainback
+// (viterbi_decoder_core.h:214-236), which all walk the same register:
+//     k = decision bit `state` of row n+K-1;  reg = (reg >> 1) | (k << top);  byte n/8 = reg >> sub
+// and of chainback_viterbi224_sse2 (viterbi224_sse2.cpp:79-121), reproduced literally.
+#include "kernels.h"
+#include "decision_layout.cuh"
+
+namespace b200v {
+
+namespace {
+
+template <int LAYOUT>
+__global__ void chainback_kernel(const ChainbackArgs a) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= a.n_frames) return;
+    const int K = a.c.K;
+    const DecisionReader<LAYOUT> rd(a, f);
+    uint8_t* out = a.out + (size_t)f * a.out_stride;
+
+    if (a.c.policy == P_KA9Q_S16_224) {
+        // no look-past-tail; emits (state & 1) into a byte that shifts right; stored when n % 8 == 0
+        unsigned state = a.endstate & ((1u << (K - 1)) - 1u);
+        unsigned dbyte = 0;
+        for (unsigned n = a.nbits; n-- > 0;) {
+            dbyte = ((state & 1u) << 7) | (dbyte >> 1);
+            if ((n & 7u) == 0) out[n >> 3] = (uint8_t)dbyte;
+            const unsigned bit = rd.bit(n, state);
+            state = (bit << (K - 2)) | (state >> 1);
+        }
+        if (a.results) a.results[f] = 0;
+        return;
+    }
+
+    const int add = (K - 1 < 8) ? 8 - (K - 1) : 0;
+    const int sub = (K - 1 > 8) ? (K - 1) - 8 : 0;
+    unsigned reg = a.endstate % (unsigned)a.c.S;
+    if (a.results) {
+        int r = 0;
+        if (a.c.policy == P_KA9Q_S16_615) r = (int)(int16_t)a.metrics[(size_t)f * a.c.S + reg];
+        a.results[f] = r;
+    }
+    reg <<= add;
+    const unsigned top = (unsigned)(K - 2 + add);
+    for (unsigned n = a.nbits; n-- > 0;) {
+        const unsigned k = rd.bit(n + (unsigned)(K - 1), reg >> add);
+        reg = (reg >> 1) | (k << top);
+        // the reference stores every iteration; the value that sticks is the one written at the lowest
+        // n of each byte, so store only there
+        if ((n & 7u) == 0) out[n >> 3] = (uint8_t)(reg >> sub);
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
+    if (a.n_frames <= 0) return cudaSuccess;
+    const int threads = 128;
+    const int blocks = (a.n_frames + threads - 1) / threads;
+    switch (a.layout) {
+    case DL_BALLOT_FRAME_MAJOR: chainback_kernel<DL_BALLOT_FRAME_MAJOR><<<blocks, threads, 0, st>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace b200v

@@ -1,0 +1,58 @@
+// kernels.h -- host-callable launchers of the CUDA kernels (one .cu per family).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "codec.h"
+
+namespace b200v {
+
+// ---- generic shared-memory ACS kernel (acs_generic.cu) -------------------------------------------
+struct GenericArgs {
+    CodecParams c;
+    const void* syms;           // device; frame f at syms + f*sym_stride bytes
+    size_t sym_stride;          // bytes
+    int nsteps;                 // steps to run in this launch
+    int step0;                  // decision row of the first step (the cursor)
+    uint32_t* dec;              // device; dec[(f*dec_rows + row)*row_words + w]
+    int dec_rows;               // rows allocated per frame
+    int row_words;              // max(2, S/32)
+    uint16_t* metrics;          // device; [n_frames][S] raw 16-bit (u8 policies zero-extended)
+    const uint8_t* cw;          // device; [S/2] code word per butterfly
+    int n_frames;
+};
+struct GenericPlan { int threads_per_frame, frames_per_block, smem_bytes; };
+GenericPlan generic_plan(const CodecParams& c);
+cudaError_t launch_acs_generic(const GenericArgs& a, cudaStream_t st);
+
+// metrics[f][s] = init_other, metrics[f][start] = init_start (all families share this buffer format)
+cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecParams& c, int starting_state,
+                                cudaStream_t st);
+
+// ---- chainback (chainback.cu) ---------------------------------------------------------------------
+struct ChainbackArgs {
+    CodecParams c;
+    int layout;                 // DecisionLayout
+    const void* dec;
+    int dec_rows, row_words;    // DL_BALLOT_FRAME_MAJOR geometry
+    int n_frames;
+    const uint16_t* metrics;    // for the KA9Q615 return value
+    uint8_t* out;               // device; frame f at out + f*out_stride
+    size_t out_stride;
+    unsigned nbits, endstate;
+    int* results;               // device [n_frames] or nullptr
+};
+cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st);
+
+// ---- synthetic input generator (generate.cu) ------------------------------------------------------
+struct GenerateArgs {
+    CodecParams c;
+    void* syms; size_t sym_stride;
+    uint8_t* data; size_t data_stride;     // may be nullptr
+    unsigned nbits;                         // data bits per frame (multiple of 8)
+    uint64_t seed, frame0;
+    int amp_q8, sigma_q8, mean_q8, lo, hi;
+    int n_frames;
+};
+cudaError_t launch_generate(const GenerateArgs& a, cudaStream_t st);
+
+}  // namespace b200v

@@ -1,0 +1,269 @@
+"""Host-side mirror of the reference's decoder interface over the C-ABI of libb200viterbi.so.
+
+The reference wraps each decoder in an adapter with ``reset() / update(sym, total_syms) /
+chainback(data, total_bits)`` (/root/reference/src/ka9q_interface.h:22-56, src/spiral_interface.h:22-56);
+:class:`BatchDecoder` offers the same three calls for a batch of independent frames, plus ``decode`` (the
+batch entry point). Everything here is ctypes plumbing: there is no Python/NumPy compute path, and loading
+fails loudly when the CUDA library is missing.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+# b200v_codec (include/b200_viterbi.h)
+KA9Q27, KA9Q29, KA9Q615, KA9Q224, SPIRAL27, SPIRAL29, SPIRAL47, SPIRAL49, SPIRAL615, WY_U8, WY_U16 = range(11)
+
+CODEC_BY_NAME = {
+    "ka9q27": KA9Q27, "ka9q29": KA9Q29, "ka9q615": KA9Q615, "ka9q224": KA9Q224,
+    "spiral27": SPIRAL27, "spiral29": SPIRAL29, "spiral47": SPIRAL47, "spiral49": SPIRAL49,
+    "spiral615": SPIRAL615, "wy_u8": WY_U8, "wy_u16": WY_U16,
+}
+
+# Polynomials the reference benchmarks (src/main.cpp:363-419) and LTE K7R3 (helpers/common_codes.h:23)
+STANDARD_POLYS = {
+    (7, 2): [0x6d, 0x4f],
+    (7, 3): [91, 117, 121],
+    (7, 4): [121, 117, 91, 111],
+    (9, 2): [0x1af, 0x11d],
+    (9, 4): [501, 441, 331, 315],
+    (15, 6): [0o42631, 0o47245, 0o56507, 0o73363, 0o77267, 0o64537],
+    (24, 2): [0o62650457, 0o62650455],
+}
+
+
+class B200ViterbiError(RuntimeError):
+    pass
+
+
+class WyConfig(C.Structure):
+    """ViterbiDecoder_Config + branch-table symbol values (b200v_wy_config)."""
+    _fields_ = [("soft_decision_high", C.c_int), ("soft_decision_low", C.c_int),
+                ("soft_decision_max_error", C.c_uint), ("initial_start_error", C.c_uint),
+                ("initial_non_start_error", C.c_uint), ("renormalisation_threshold", C.c_uint)]
+
+
+_lib = None
+
+
+def library_path():
+    return _build.LIB_PATH
+
+
+def load_library():
+    """dlopen libb200viterbi.so (building it first if the sources are newer). No fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path) or (_build.nvcc_path() and _build.needs_build()):
+        _build.build_library()
+    if not os.path.exists(path):
+        raise B200ViterbiError(f"{path} is missing and cannot be built: the CUDA extension is required")
+    lib = C.CDLL(path)
+    vp, sz, i32, u32, u64 = C.c_void_p, C.c_size_t, C.c_int, C.c_uint, C.c_uint64
+    sig = {
+        "b200v_version": (i32, []),
+        "b200v_last_error": (C.c_char_p, []),
+        "b200v_device_count": (i32, []),
+        "b200v_codec_shape": (i32, [i32, C.POINTER(i32), C.POINTER(i32)]),
+        "b200v_codec_symbol_bytes": (i32, [i32]),
+        "b200v_codec_metric_bytes": (i32, [i32]),
+        "b200v_batch_create": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, i32, C.POINTER(WyConfig)]),
+        "b200v_batch_destroy": (None, [vp]),
+        "b200v_batch_set_stream": (i32, [vp, vp]),
+        "b200v_batch_set_variant": (i32, [vp, i32]),
+        "b200v_batch_get_variant": (i32, [vp]),
+        "b200v_batch_init": (i32, [vp, i32]),
+        "b200v_batch_update_dev": (i32, [vp, vp, sz, i32]),
+        "b200v_batch_update": (i32, [vp, vp, sz, i32]),
+        "b200v_batch_chainback_dev": (i32, [vp, vp, sz, u32, u32]),
+        "b200v_batch_chainback": (i32, [vp, vp, sz, u32, u32]),
+        "b200v_batch_chainback_results": (i32, [vp, vp]),
+        "b200v_batch_decode": (i32, [vp, vp, vp, u32]),
+        "b200v_batch_sync": (i32, [vp]),
+        "b200v_batch_get_decisions": (i32, [vp, i32, i32, i32, vp]),
+        "b200v_batch_get_metrics": (i32, [vp, i32, vp]),
+        "b200v_batch_steps_done": (i32, [vp]),
+        "b200v_batch_last_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+        "b200v_batch_launch_count": (C.c_longlong, [vp]),
+        "b200v_batch_generate_dev": (i32, [vp, vp, sz, vp, sz, u32, u64, u64, i32, i32, i32, i32, i32]),
+        "b200v_device_alloc": (vp, [i32, sz]),
+        "b200v_device_free": (None, [i32, vp]),
+        "b200v_host_alloc_pinned": (vp, [sz]),
+        "b200v_host_free_pinned": (None, [vp]),
+        "b200v_memcpy_h2d": (i32, [i32, vp, vp, sz]),
+        "b200v_memcpy_d2h": (i32, [i32, vp, vp, sz]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = [
+    "b200v_version", "b200v_last_error", "b200v_device_count", "b200v_codec_shape",
+    "b200v_codec_symbol_bytes", "b200v_codec_metric_bytes", "b200v_batch_create", "b200v_batch_destroy",
+    "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_init",
+    "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
+    "b200v_batch_chainback_results", "b200v_batch_decode", "b200v_batch_sync", "b200v_batch_get_decisions",
+    "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
+    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_device_alloc", "b200v_device_free",
+    "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
+]
+
+
+def _check(rc):
+    if rc != 0:
+        raise B200ViterbiError(f"b200v error {rc}: {load_library().b200v_last_error().decode()}")
+
+
+def symbol_dtype(codec):
+    return {WY_U8: np.int8, WY_U16: np.int16}.get(codec, np.uint8)
+
+
+def metric_dtype(codec):
+    return {KA9Q615: np.int16, KA9Q224: np.int16, WY_U16: np.uint16}.get(codec, np.uint8)
+
+
+def _ptr(x):
+    """Device pointer of a torch tensor / raw int, or host pointer of a numpy array."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    return x.data_ptr()   # torch.Tensor
+
+
+class BatchDecoder:
+    """n_frames independent frames of one codec on one GPU.
+
+    ``frame_steps`` is the number of trellis steps per frame including the K-1 tail steps -- the ``len`` the
+    reference's adapters pass to ``create_*`` (src/ka9q_interface.h:28, src/main.cpp:247).
+    """
+
+    def __init__(self, codec, frame_steps, n_frames=1, K=0, R=0, poly=None, device=0, wy_config=None):
+        self.lib = load_library()
+        if isinstance(codec, str):
+            codec = CODEC_BY_NAME[codec]
+        self.codec = codec
+        k, r = C.c_int(0), C.c_int(0)
+        _check(self.lib.b200v_codec_shape(codec, C.byref(k), C.byref(r)))
+        self.K = k.value or K
+        self.R = r.value or R
+        if poly is None:
+            poly = STANDARD_POLYS.get((self.K, self.R))
+            if poly is None:
+                raise ValueError(f"no standard polynomials for K={self.K} R={self.R}")
+        self.poly = list(poly)
+        self.S = 1 << (self.K - 1)
+        self.frame_steps, self.n_frames, self.device = frame_steps, n_frames, device
+        self.sym_dtype = symbol_dtype(codec)
+        arr = (C.c_int * len(self.poly))(*self.poly)
+        cfg = C.byref(wy_config) if wy_config is not None else None
+        self.h = self.lib.b200v_batch_create(codec, self.K, self.R, arr, frame_steps, n_frames, device, cfg)
+        if not self.h:
+            raise B200ViterbiError("b200v_batch_create failed: " + self.lib.b200v_last_error().decode())
+
+    # -- the reference adapter's three calls, batched ------------------------------------------------
+    def reset(self, starting_state=0):
+        _check(self.lib.b200v_batch_init(self.h, starting_state))
+
+    def update(self, sym, total_syms=None):
+        """sym: host array [n_frames, total_syms] (or flat for one frame). total_syms must be a multiple of R."""
+        sym = np.ascontiguousarray(sym, dtype=self.sym_dtype).reshape(self.n_frames, -1)
+        if total_syms is None:
+            total_syms = sym.shape[1]
+        if total_syms % self.R:
+            raise ValueError("total_syms must be a multiple of the code rate")   # ka9q_interface.h:49
+        _check(self.lib.b200v_batch_update(self.h, sym.ctypes.data, sym.strides[0], total_syms // self.R))
+
+    def chainback(self, total_bits, endstate=0):
+        out = np.zeros((self.n_frames, (total_bits + 7) // 8), dtype=np.uint8)
+        _check(self.lib.b200v_batch_chainback(self.h, out.ctypes.data, out.strides[0], total_bits, endstate))
+        return out
+
+    # -- batch entry point ----------------------------------------------------------------------------
+    def decode(self, sym, total_bits):
+        sym = np.ascontiguousarray(sym, dtype=self.sym_dtype).reshape(self.n_frames, -1)
+        assert sym.shape[1] == self.frame_steps * self.R
+        out = np.zeros((self.n_frames, (total_bits + 7) // 8), dtype=np.uint8)
+        _check(self.lib.b200v_batch_decode(self.h, sym.ctypes.data, out.ctypes.data, total_bits))
+        return out
+
+    # -- device-pointer variants (inputs already in HBM) ------------------------------------------------
+    def update_dev(self, d_syms, frame_stride_bytes, nsteps):
+        _check(self.lib.b200v_batch_update_dev(self.h, _ptr(d_syms), frame_stride_bytes, nsteps))
+
+    def chainback_dev(self, d_out, frame_stride_bytes, total_bits, endstate=0):
+        _check(self.lib.b200v_batch_chainback_dev(self.h, _ptr(d_out), frame_stride_bytes, total_bits, endstate))
+
+    def generate_dev(self, d_syms, sym_stride, d_data, data_stride, nbits, seed, frame0, amp_q8, sigma_q8,
+                     mean_q8, lo, hi):
+        _check(self.lib.b200v_batch_generate_dev(self.h, _ptr(d_syms), sym_stride, _ptr(d_data), data_stride,
+                                                 nbits, seed, frame0, amp_q8, sigma_q8, mean_q8, lo, hi))
+
+    def set_stream(self, cuda_stream):
+        _check(self.lib.b200v_batch_set_stream(self.h, cuda_stream))
+
+    def set_variant(self, variant):
+        _check(self.lib.b200v_batch_set_variant(self.h, variant))
+
+    @property
+    def variant(self):
+        return self.lib.b200v_batch_get_variant(self.h)
+
+    def sync(self):
+        _check(self.lib.b200v_batch_sync(self.h))
+
+    # -- introspection -----------------------------------------------------------------------------------
+    def chainback_results(self):
+        out = np.zeros(self.n_frames, dtype=np.int32)
+        _check(self.lib.b200v_batch_chainback_results(self.h, out.ctypes.data))
+        return out
+
+    def decisions(self, frame, step0, nsteps):
+        out = np.zeros((nsteps, self.S // 8), dtype=np.uint8)
+        _check(self.lib.b200v_batch_get_decisions(self.h, frame, step0, nsteps, out.ctypes.data))
+        return out
+
+    def metrics(self, frame):
+        out = np.zeros(self.S, dtype=metric_dtype(self.codec))
+        _check(self.lib.b200v_batch_get_metrics(self.h, frame, out.ctypes.data))
+        return out
+
+    @property
+    def steps_done(self):
+        return self.lib.b200v_batch_steps_done(self.h)
+
+    def last_kernel_ms(self):
+        u, c = C.c_float(0), C.c_float(0)
+        _check(self.lib.b200v_batch_last_kernel_ms(self.h, C.byref(u), C.byref(c)))
+        return u.value, c.value
+
+    @property
+    def launch_count(self):
+        return self.lib.b200v_batch_launch_count(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200v_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

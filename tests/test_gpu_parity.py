@@ -1,0 +1,284 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the oracle on identical inputs, bit-exact on
+per-step decision vectors, final path metrics, decoded bytes and chainback return values; against the
+golden vectors generated from the compiled reference; and, at full size, through round-trip properties."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import _oracle as o
+import ka9q_viterbi_comparison_b200 as kv
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.npz")
+
+# oracle registry name -> (b200v codec, K, R)
+CASES = {
+    "ka9q27": (kv.KA9Q27, 7, 2), "ka9q29": (kv.KA9Q29, 9, 2), "ka9q615": (kv.KA9Q615, 15, 6),
+    "spiral27": (kv.SPIRAL27, 7, 2), "spiral29": (kv.SPIRAL29, 9, 2), "spiral47": (kv.SPIRAL47, 7, 4),
+    "spiral49": (kv.SPIRAL49, 9, 4), "spiral615": (kv.SPIRAL615, 15, 6),
+    "wy_sse_u8_k7r2": (kv.WY_U8, 7, 2), "wy_sse_u16_k7r2": (kv.WY_U16, 7, 2),
+    "wy_sse_u8_k7r3": (kv.WY_U8, 7, 3), "wy_sse_u16_k7r3": (kv.WY_U16, 7, 3),
+    "wy_sse_u8_k7r4": (kv.WY_U8, 7, 4), "wy_sse_u16_k7r4": (kv.WY_U16, 7, 4),
+    "wy_sse_u8_k9r2": (kv.WY_U8, 9, 2), "wy_sse_u16_k9r2": (kv.WY_U16, 9, 2),
+    "wy_sse_u8_k9r4": (kv.WY_U8, 9, 4), "wy_sse_u16_k9r4": (kv.WY_U16, 9, 4),
+    "wy_sse_u8_k15r6": (kv.WY_U8, 15, 6), "wy_sse_u16_k15r6": (kv.WY_U16, 15, 6),
+}
+
+
+def sha(a):
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), dtype=np.uint8)
+
+
+def make_batch(c, n_frames, nbytes, sigma, seed):
+    rows, datas = [], []
+    for f in range(n_frames):
+        d, s = o.make_frame(c, nbytes, sigma, seed=seed, frame=f)
+        rows.append(s)
+        datas.append(d)
+    return np.stack(datas), np.stack(rows)
+
+
+def variants(dec):
+    """Kernel families available for this instance (1 = generic always; 2 = specialised when present)."""
+    out = [1]
+    try:
+        dec.set_variant(2)
+        out.append(2)
+    except kv.B200ViterbiError:
+        pass
+    return out
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_matches_golden_reference_vectors(name):
+    """Known answers produced by the unmodified reference (tests/golden/make_golden.py)."""
+    g = np.load(GOLDEN)
+    codec, K, R = CASES[name]
+    for ci in range(3):
+        key = f"{name}/{ci}"
+        syms = g[key + "/syms"]
+        T = syms.size // R
+        nbits = T - (K - 1)
+        with kv.BatchDecoder(codec, T, 1, K=K, R=R) as dec:
+            for v in variants(dec):
+                dec.set_variant(v)
+                dec.reset()
+                dec.update(syms)
+                out = dec.chainback(nbits)[0]
+                assert np.array_equal(out, g[key + "/out"]), f"{key} v{v}: decoded bytes"
+                assert int(dec.chainback_results()[0]) == int(g[key + "/rc"]), f"{key} v{v}: return value"
+                assert np.array_equal(sha(dec.decisions(0, 0, T)), g[key + "/dec_sha256"]), f"{key} v{v}: decisions"
+                assert np.array_equal(sha(dec.metrics(0)), g[key + "/metrics_sha256"]), f"{key} v{v}: metrics"
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("sigma", [0.0, 0.7, 1.0])
+def test_batch_matches_oracle(name, sigma):
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes = 8 if K == 15 else 48
+    n_frames = 5 if K == 15 else 37       # ragged vs block/warp sizes on purpose
+    T = nbytes * 8 + K - 1
+    data, syms = make_batch(c, n_frames, nbytes, sigma, seed=0x5EED)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        for v in variants(dec):
+            dec.set_variant(v)
+            out = dec.decode(syms, nbytes * 8)
+            rcs = dec.chainback_results()
+            for f in range(n_frames):
+                q = o.Oracle(c, T)
+                q.init(0)
+                q.update(syms[f], T)
+                qo, qrc = q.chainback(nbytes * 8, 0, return_code=True)
+                assert np.array_equal(dec.decisions(f, 0, T), q.decisions(0, T)), f"v{v} frame {f}: decisions"
+                assert np.array_equal(dec.metrics(f), q.metrics()), f"v{v} frame {f}: metrics"
+                assert np.array_equal(out[f], qo), f"v{v} frame {f}: decoded bytes"
+                assert int(rcs[f]) == qrc
+                if sigma == 0.0:
+                    assert np.array_equal(out[f], data[f])
+                q.close()
+
+
+@pytest.mark.parametrize("name", ["ka9q27", "ka9q29", "wy_sse_u8_k7r2", "wy_sse_u16_k9r4", "ka9q615"])
+def test_streaming_update_matches_oracle(name):
+    """update() in blocks of arbitrary size continues where the previous call stopped."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes = 8 if K == 15 else 40
+    T = nbytes * 8 + K - 1
+    n_frames = 3
+    data, syms = make_batch(c, n_frames, nbytes, 0.8, seed=11)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        for v in variants(dec):
+            dec.set_variant(v)
+            dec.reset()
+            pos = 0
+            for chunk in (1, 2, 5, 17, 64, T):
+                n = min(chunk, T - pos)
+                if n == 0:
+                    break
+                dec.update(syms[:, pos * R:(pos + n) * R])
+                pos += n
+                assert dec.steps_done == pos
+            out = dec.chainback(nbytes * 8)
+            for f in range(n_frames):
+                q = o.Oracle(c, T)
+                qo, qd = q.decode(syms[f], nbytes * 8)
+                assert np.array_equal(dec.decisions(f, 0, T), qd)
+                assert np.array_equal(out[f], qo)
+                q.close()
+
+
+def test_spiral_update_restarts_and_drops_odd_step():
+    """spiral27.cpp:383-386: every update starts at decision row 0 and runs nbits/2 double steps."""
+    c = o.codec_by_name("spiral27")
+    nbytes, K, R = 16, 7, 2
+    T = nbytes * 8 + K - 1
+    data, syms = make_batch(c, 2, nbytes, 0.6, seed=3)
+    with kv.BatchDecoder(kv.SPIRAL27, T, 2) as dec:
+        dec.reset()
+        dec.update(syms[:, :(T - 1) * R])        # odd number of steps: the last one is dropped
+        assert dec.steps_done == T - 2
+        q = o.Oracle(c, T)
+        q.init(0)
+        q.update(syms[0], T - 1)
+        assert np.array_equal(dec.decisions(0, 0, T - 2), q.decisions(0, T - 2))
+        assert np.array_equal(dec.metrics(0), q.metrics())
+        q.close()
+
+
+def test_extreme_symbol_patterns():
+    """Saturation, ties on every butterfly and frequent renormalisation."""
+    for name in ["ka9q27", "spiral27", "spiral47", "spiral29", "wy_sse_u8_k7r2", "wy_sse_u16_k7r4",
+                 "spiral615", "ka9q615", "wy_sse_u8_k15r6"]:
+        codec, K, R = CASES[name]
+        c = o.codec_by_name(name)
+        lo, hi = o.soft_range(c)
+        T = 120 if K == 15 else 600
+        n = T * R
+        pats = np.stack([np.full(n, lo), np.full(n, hi), np.where(np.arange(n) % 2, lo, hi),
+                         np.full(n, (lo + hi) // 2), np.where((np.arange(n) // R) % 3 == 0, hi, lo)])
+        pats = pats.astype(o.sym_dtype(c))
+        nbits = T - (K - 1)
+        with kv.BatchDecoder(codec, T, pats.shape[0], K=K, R=R) as dec:
+            for v in variants(dec):
+                dec.set_variant(v)
+                dec.reset()
+                dec.update(pats)
+                out = dec.chainback(nbits)
+                for f in range(pats.shape[0]):
+                    q = o.Oracle(c, T)
+                    qo, qd = q.decode(pats[f], nbits)
+                    assert np.array_equal(dec.decisions(f, 0, T), qd), (name, v, f)
+                    assert np.array_equal(dec.metrics(f), q.metrics()), (name, v, f)
+                    assert np.array_equal(out[f], qo), (name, v, f)
+                    q.close()
+
+
+def test_nonstandard_polynomials_and_start_state():
+    """Per-instance branch tables (any polynomial), non-zero starting / end states, negative spiral poly."""
+    cases = [("ka9q27", kv.KA9Q27, 7, 2, [0o171, 0o133]), ("spiral27", kv.SPIRAL27, 7, 2, [-0x6d, 0x4f]),
+             ("wy_sse_u8_k7r3", kv.WY_U8, 7, 3, [0o133, 0o171, 0o165]), ("ka9q29", kv.KA9Q29, 9, 2, [0o753, 0o561])]
+    for name, codec, K, R, poly in cases:
+        c = o.codec_by_name(name, poly=poly)
+        nbytes = 24
+        T = nbytes * 8 + K - 1
+        data, syms = make_batch(c, 4, nbytes, 0.7, seed=99)
+        with kv.BatchDecoder(codec, T, 4, K=K, R=R, poly=poly) as dec:
+            dec.reset(5)
+            dec.update(syms)
+            out = dec.chainback(nbytes * 8, endstate=3)
+            for f in range(4):
+                q = o.Oracle(c, T)
+                q.init(5)
+                q.update(syms[f], T)
+                assert np.array_equal(dec.decisions(f, 0, T), q.decisions(0, T)), name
+                assert np.array_equal(out[f], q.chainback(nbytes * 8, 3)), name
+                q.close()
+
+
+def test_partial_byte_and_empty_calls():
+    c = o.codec_by_name("ka9q27")
+    nbytes, K, R = 12, 7, 2
+    T = nbytes * 8 + K - 1
+    data, syms = make_batch(c, 2, nbytes, 0.5, seed=5)
+    with kv.BatchDecoder(kv.KA9Q27, T, 2) as dec:
+        dec.reset()
+        dec.update(syms[:, :0])                  # zero steps: a no-op
+        assert dec.steps_done == 0
+        dec.update(syms)
+        q = o.Oracle(c, T)
+        q.init(0)
+        q.update(syms[1], T)
+        for nbits in (1, 7, 13, nbytes * 8 - 3):
+            assert np.array_equal(dec.chainback(nbits)[1], q.chainback(nbits)), nbits
+        q.close()
+        with pytest.raises(kv.B200ViterbiError):
+            dec.update(syms)                     # past the allocated decision rows
+
+
+def test_device_generator_matches_host_generator():
+    """b200v_batch_generate_dev (encoder + integer AWGN channel) == the oracle-side generator, bit for bit."""
+    import torch
+    for name in ["ka9q27", "spiral49", "wy_sse_u8_k7r3", "wy_sse_u16_k15r6"]:
+        codec, K, R = CASES[name]
+        c = o.codec_by_name(name)
+        nbytes, n_frames, frame0, seed = 16, 9, 1000, 0xB200
+        T = nbytes * 8 + K - 1
+        for sigma in (0.0, 0.8):
+            amp_q8, sigma_q8, mean_q8, lo, hi = o.channel_params(c, sigma)
+            with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+                sb = c_sym_bytes = np.dtype(o.sym_dtype(c)).itemsize
+                d_syms = torch.zeros(n_frames * T * R * sb, dtype=torch.uint8, device="cuda")
+                d_data = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
+                dec.generate_dev(d_syms, T * R * sb, d_data, nbytes, nbytes * 8, seed, frame0, amp_q8, sigma_q8,
+                                 mean_q8, lo, hi)
+                dec.sync()
+                got_syms = d_syms.cpu().numpy().view(o.sym_dtype(c)).reshape(n_frames, T * R)
+                got_data = d_data.cpu().numpy().reshape(n_frames, nbytes)
+                for f in range(n_frames):
+                    data, syms = o.make_frame(c, nbytes, sigma, seed=seed, frame=frame0 + f)
+                    assert np.array_equal(got_data[f], data), (name, sigma, f)
+                    assert np.array_equal(got_syms[f], syms), (name, sigma, f)
+
+
+def test_full_size_round_trip_properties():
+    """BASELINE configs[1]-sized frames (2048 bits), large batch, inputs generated on the device:
+    noiseless encode -> decode returns the data exactly; a second identical run is bit-identical
+    (determinism); decoded output of noisy frames has low BER."""
+    import torch
+    name, codec, K, R = "ka9q27", kv.KA9Q27, 7, 2
+    c = o.codec_by_name(name)
+    nbits, n_frames = 2048, 16384
+    T = nbits + K - 1
+    with kv.BatchDecoder(codec, T, n_frames) as dec:
+        d_syms = torch.empty(n_frames * T * R, dtype=torch.uint8, device="cuda")
+        d_data = torch.empty(n_frames * nbits // 8, dtype=torch.uint8, device="cuda")
+        d_out = torch.empty(n_frames * nbits // 8, dtype=torch.uint8, device="cuda")
+        for sigma in (0.0, 0.6):
+            amp_q8, sigma_q8, mean_q8, lo, hi = o.channel_params(c, sigma)
+            dec.generate_dev(d_syms, T * R, d_data, nbits // 8, nbits, 1234, 0, amp_q8, sigma_q8, mean_q8, lo, hi)
+            outs = []
+            for _ in range(2):
+                dec.reset()
+                dec.update_dev(d_syms, T * R, T)
+                dec.chainback_dev(d_out, nbits // 8, nbits)
+                dec.sync()
+                outs.append(d_out.clone())
+            assert torch.equal(outs[0], outs[1])
+            errs = (outs[0] ^ d_data).cpu().numpy()
+            ber = np.unpackbits(errs).mean()
+            if sigma == 0.0:
+                assert ber == 0.0
+            else:
+                assert ber < 1e-3, ber
+            # spot-check 3 frames against the oracle
+            syms = d_syms.cpu().numpy().reshape(n_frames, T * R)
+            for f in (0, n_frames // 2, n_frames - 1):
+                q = o.Oracle(c, T)
+                qo, _ = q.decode(syms[f], nbits)
+                assert np.array_equal(outs[0].cpu().numpy().reshape(n_frames, -1)[f], qo)
+                q.close()
