@@ -1,0 +1,399 @@
+// acs_k7.cu -- register-resident add-compare-select for K=7 (64 states): one thread per frame, metrics as
+// u16x2 pairs in 32 registers updated in place (see acs_k7.cuh for the index algebra), DPX instructions
+// (VIADDMNMX.U16x2 / VIMNMX.U16x2 with predicate outputs) for saturating add and compare-select, decisions
+// of a step packed into one u64 and written frame-interleaved (dec[row][frame]) so that both this kernel's
+// stores and the chainback kernel's loads are coalesced.
+//
+// Specialised at compile time on (policy, R, polynomials) so that every register index and every
+// branch-metric selection is static. Takes the role of update_viterbi27_blk_sse2
+// (ka9q_libfec_port/viterbi27_sse2.cpp:119-175), update_spiral27/47 (spiral/spiral27.cpp:130-386,
+// spiral47.cpp) and ViterbiDecoder_SSE_u8<7,R>::update (viterbi/x86/viterbi_decoder_sse_u8.h:45-154).
+//
+// Bit-exactness notes
+//  * saturating policies (spiral, wy-u8): registers hold true_metric + off, where `off` is a per-frame
+//    offset; the reference's "subtract the minimum when new[0] crosses the threshold" becomes off = min(w),
+//    and saturation at 255 becomes a clamp at 255 + off, so no per-frame divergent subtract pass is needed.
+//  * ka9q modular policy: registers hold the unwrapped metric U (reference metric = U mod 256). The
+//    reference decides with (int8)(m0 - m1) > 0; for K=7 the difference of the two candidates is bounded by
+//    113 < 128 for every possible input (max metric <= 63 + 7t for t <= 6 because the two branches into a
+//    state cost bm and 15-bm; spread <= 90 afterwards), so the modular compare equals the plain compare.
+#include "kernels.h"
+#include "acs_k7.cuh"
+#include "policy.cuh"
+
+namespace b200v {
+namespace k7 {
+
+template <int R_, int P0, int P1, int P2, int P3>
+struct Code {
+    static constexpr int R = R_;
+    __host__ __device__ static constexpr int poly(int i) { return i == 0 ? P0 : i == 1 ? P1 : i == 2 ? P2 : P3; }
+    __host__ __device__ static constexpr int cw(int j) {
+        int c = 0;
+        for (int i = 0; i < R; i++) c |= parity_of((unsigned)(2 * j) & (unsigned)poly(i)) << i;
+        return c;
+    }
+};
+
+__device__ __forceinline__ uint32_t pack2(uint32_t lo, uint32_t hi) { return lo | (hi << 16); }
+
+// s = min(a, b) per u16 lane (VIMNMX.U16x2 with predicate outputs); decision of a lane = (a <= b), or its
+// negation when NEG; a set decision ORs the lane's bit into acc with one predicated LOP3. Written as one PTX
+// block so that ptxas keeps the predicates (the C++ form costs a clear + a set per decision).
+template <int BIT_LO, int BIT_HI, bool NEG>
+__device__ __forceinline__ uint32_t min_acc(uint32_t a, uint32_t b, uint32_t& acc) {
+    uint32_t s;
+    if (NEG) {
+        asm("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+            "min.u16x2 %0, %2, %3;\n\t"
+            "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %2;\n\t"
+            "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
+            "@!pv or.b32 %1, %1, %4;\n\t@!pu or.b32 %1, %1, %5;\n\t}"
+            : "=&r"(s), "+r"(acc) : "r"(a), "r"(b), "n"(1u << BIT_LO), "n"(1u << BIT_HI));
+    } else {
+        asm("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+            "min.u16x2 %0, %2, %3;\n\t"
+            "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %2;\n\t"
+            "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
+            "@pv or.b32 %1, %1, %4;\n\t@pu or.b32 %1, %1, %5;\n\t}"
+            : "=&r"(s), "+r"(acc) : "r"(a), "r"(b), "n"(1u << BIT_LO), "n"(1u << BIT_HI));
+    }
+    return s;
+}
+
+template <int POLICY>
+struct Arith {
+    static constexpr bool modular = (POLICY == P_KA9Q_U8_MOD);
+    // candidate = old + branch metric (saturating at the clamp for the u8-saturating policies)
+    __device__ __forceinline__ static uint32_t add(uint32_t a, uint32_t w, uint32_t clamp) {
+        if (modular) return a + w;                 // lanes never overflow (rebased every 64 periods)
+        return __viaddmin_u16x2(a, w, clamp);
+    }
+};
+
+// scalar branch metric and complement for code word CW (compile-time), symbols sym[R]
+template <int POLICY, int R, int CW>
+__device__ __forceinline__ void bm_pair(const int* sym, int C, int soft_hi, int soft_lo, uint32_t& bm, uint32_t& cm) {
+    int v;
+    if (POLICY == P_WY_U8) {
+        int tot = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int bt = ((CW >> i) & 1) ? soft_hi : soft_lo;
+            int e = clamp_i(bt - sym[i], -128, 127);
+            tot = min(tot + abs(e), 255);
+        }
+        v = tot;
+    } else if (POLICY == P_KA9Q_U8_MOD || POLICY == P_SPIRAL_R2) {
+        const int x0 = (CW & 1) ? (sym[0] ^ 255) : sym[0];
+        const int x1 = (CW & 2) ? (sym[1] ^ 255) : sym[1];
+        const int avg = (x0 + x1 + 1) >> 1;
+        v = POLICY == P_KA9Q_U8_MOD ? (avg >> 4) : ((avg >> 2) & 63);
+    } else {   // P_SPIRAL_R4
+        int s = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int x = ((CW >> i) & 1) ? (sym[i] ^ 255) : sym[i];
+            s = min(s + ((x >> 2) & 63), 255);
+        }
+        v = (s >> 2) & 63;
+    }
+    bm = (uint32_t)v;
+    cm = (uint32_t)max(C - v, 0);
+}
+
+template <int POLICY, class CODE, int CW, int NCW>
+struct BmFill {
+    __device__ __forceinline__ static void run(const int* sym, int C, int hi, int lo, uint32_t* bm, uint32_t* cm) {
+        bm_pair<POLICY, CODE::R, CW>(sym, C, hi, lo, bm[CW], cm[CW]);
+        BmFill<POLICY, CODE, CW + 1, NCW>::run(sym, C, hi, lo, bm, cm);
+    }
+};
+template <int POLICY, class CODE, int NCW>
+struct BmFill<POLICY, CODE, NCW, NCW> {
+    __device__ __forceinline__ static void run(const int*, int, int, int, uint32_t*, uint32_t*) {}
+};
+
+struct K7Args {
+    const unsigned char* syms; size_t sym_stride;
+    int nsteps, step0;
+    unsigned long long* dec;       // dec[row * n_frames + frame]
+    uint8_t* row_phase;            // phase of the step that produced each row
+    uint16_t* metrics;             // canonical [n_frames][64] (reference metric values)
+    int n_frames;
+    int C, thr, soft_hi, soft_lo;
+};
+
+// ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
+template <int POLICY, class CODE, int P, int KK>
+struct PairLoop {
+    __device__ __forceinline__ static void run(uint32_t (&w)[NW], const uint32_t* W, const uint32_t* Wc,
+                                               uint32_t clamp, uint32_t& acc0, uint32_t& acc1) {
+        constexpr int XB = NB - 2 - P;                         // register-index bit that holds the state MSB
+        constexpr int iA = expand_bit(KK, XB), iB = iA | (1 << XB);
+        constexpr int c = CODE::cw(logical_of(P, iA << 1));
+        const uint32_t A = w[iA], B = w[iB];
+        const uint32_t m0 = Arith<POLICY>::add(A, W[c], clamp), m1 = Arith<POLICY>::add(B, Wc[c], clamp);
+        const uint32_t m2 = Arith<POLICY>::add(A, Wc[c], clamp), m3 = Arith<POLICY>::add(B, W[c], clamp);
+        if (Arith<POLICY>::modular) {      // decision = (lo path > hi path), tie -> 0 (viterbi27_sse2.cpp:155-158)
+            w[iA] = min_acc<KK, 16 + KK, true>(m0, m1, acc0);
+            w[iB] = min_acc<KK, 16 + KK, true>(m2, m3, acc1);
+        } else {                           // decision = (min == hi path), tie -> 1 (spiral27.cpp:178-181)
+            w[iA] = min_acc<KK, 16 + KK, false>(m1, m0, acc0);
+            w[iB] = min_acc<KK, 16 + KK, false>(m3, m2, acc1);
+        }
+        PairLoop<POLICY, CODE, P, KK + 1>::run(w, W, Wc, clamp, acc0, acc1);
+    }
+};
+template <int POLICY, class CODE, int P>
+struct PairLoop<POLICY, CODE, P, 16> {
+    __device__ __forceinline__ static void run(uint32_t (&)[NW], const uint32_t*, const uint32_t*, uint32_t,
+                                               uint32_t&, uint32_t&) {}
+};
+
+// last phase: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
+template <int POLICY, class CODE, int I>
+struct InRegLoop {
+    __device__ __forceinline__ static void run(uint32_t (&w)[NW], const uint32_t* bm, const uint32_t* cm,
+                                               uint32_t clamp, uint32_t& acc0, uint32_t& acc1) {
+        constexpr int c = CODE::cw(I);
+        const uint32_t x = w[I];
+        const uint32_t ma = Arith<POLICY>::add(x, bm[c] * 0x10001u, clamp);   // (m0, m3)
+        const uint32_t mb = Arith<POLICY>::add(x, cm[c] * 0x10001u, clamp);   // (m2, m1)
+        const uint32_t lo_paths = __byte_perm(ma, mb, 0x5410);               // (m0, m2)
+        const uint32_t hi_paths = __byte_perm(mb, ma, 0x7632);               // (m1, m3)
+        uint32_t& acc = (I < 16) ? acc0 : acc1;
+        if (Arith<POLICY>::modular) w[I] = min_acc<(I & 15), 16 + (I & 15), true>(lo_paths, hi_paths, acc);
+        else w[I] = min_acc<(I & 15), 16 + (I & 15), false>(hi_paths, lo_paths, acc);
+        InRegLoop<POLICY, CODE, I + 1>::run(w, bm, cm, clamp, acc0, acc1);
+    }
+};
+template <int POLICY, class CODE>
+struct InRegLoop<POLICY, CODE, NW> {
+    __device__ __forceinline__ static void run(uint32_t (&)[NW], const uint32_t*, const uint32_t*, uint32_t,
+                                               uint32_t&, uint32_t&) {}
+};
+
+// ---- one trellis step in phase P -------------------------------------------------------------------
+template <int POLICY, class CODE, int P>
+__device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7Args& a, uint32_t& off,
+                                     unsigned long long* dec_out) {
+    constexpr int R = CODE::R, NCW = 1 << R;
+    uint32_t bm[NCW], cm[NCW];
+    BmFill<POLICY, CODE, 0, NCW>::run(sym, a.C, a.soft_hi, a.soft_lo, bm, cm);
+    const uint32_t clamp = (255u + off) * 0x10001u;
+    uint32_t acc0 = 0, acc1 = 0;
+
+    if constexpr (P < NB - 1) {
+        constexpr int DELTA = CODE::cw(1 << P);            // lane 1 holds butterfly j | (1 << P)
+        uint32_t W[NCW], Wc[NCW];
+#pragma unroll
+        for (int c = 0; c < NCW; c++) { W[c] = pack2(bm[c], bm[c ^ DELTA]); Wc[c] = pack2(cm[c], cm[c ^ DELTA]); }
+        PairLoop<POLICY, CODE, P, 0>::run(w, W, Wc, clamp, acc0, acc1);
+    } else {
+        // in-register butterflies: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
+        InRegLoop<POLICY, CODE, 0>::run(w, bm, cm, clamp, acc0, acc1);
+    }
+    *dec_out = (unsigned long long)acc0 | ((unsigned long long)acc1 << 32);
+
+    // renormalisation (saturating policies): new[0] is always register 0, lane 0
+    if (!Arith<POLICY>::modular) {
+        uint32_t mn = __vimin3_u16x2(w[0], w[1], w[2]);
+#pragma unroll
+        for (int i = 3; i + 1 < NW; i += 2) mn = __vimin3_u16x2(mn, w[i], w[i + 1]);
+        mn = __vminu2(mn, w[NW - 1]);
+        const uint32_t m = min(mn & 0xffffu, mn >> 16);
+        const int true0 = (int)(w[0] & 0xffffu) - (int)off;
+        const bool need = (POLICY == P_WY_U8) ? (true0 >= a.thr) : (true0 > a.thr);
+        if (need) off = m;
+    }
+}
+
+// ---- symbol fetch: one period (6 steps * R bytes) per frame into registers ---------------------------
+template <int R> struct PeriodBuf {
+    static constexpr int BYTES = NB * R;
+    static constexpr int WORDS = (BYTES + 3) / 4;
+    uint32_t w[WORDS];
+    __device__ __forceinline__ void load(const unsigned char* p) {
+        if ((BYTES % 4 == 0) && ((reinterpret_cast<uintptr_t>(p) & 3) == 0)) {
+#pragma unroll
+            for (int i = 0; i < WORDS; i++) w[i] = __ldg(reinterpret_cast<const uint32_t*>(p) + i);
+        } else {
+#pragma unroll
+            for (int i = 0; i < WORDS; i++) {
+                uint32_t v = 0;
+#pragma unroll
+                for (int b = 0; b < 4; b++)
+                    if (i * 4 + b < BYTES) v |= (uint32_t)__ldg(p + i * 4 + b) << (8 * b);
+                w[i] = v;
+            }
+        }
+    }
+    template <int POLICY>
+    __device__ __forceinline__ void symbols(int step, int* sym) const {
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int b = step * R + i;
+            const uint32_t v = (w[b >> 2] >> ((b & 3) * 8)) & 0xffu;
+            sym[i] = (POLICY == P_WY_U8) ? (int)(int8_t)v : (int)v;
+        }
+    }
+};
+
+template <int POLICY, class CODE, int P>
+__device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE::R>& buf, const K7Args& a,
+                                         uint32_t& off, unsigned long long* dec_row) {
+    int sym[CODE::R];
+    buf.template symbols<POLICY>(P, sym);
+    step<POLICY, CODE, P>(w, sym, a, off, dec_row);
+}
+
+template <int POLICY, class CODE>
+__global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
+    constexpr int R = CODE::R;
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x == 0) {   // phase of every decision row this launch writes (read by chainback)
+        for (int t = threadIdx.x; t < a.nsteps; t += blockDim.x) a.row_phase[a.step0 + t] = (uint8_t)(t % NB);
+    }
+    if (f >= a.n_frames) return;
+
+    // ---- load canonical metrics into the phase-0 layout: register i = states (2i, 2i+1) ----
+    uint32_t w[NW];
+    uint32_t off = 0;
+    {
+        const uint32_t* g = reinterpret_cast<const uint32_t*>(a.metrics + (size_t)f * S);
+#pragma unroll
+        for (int i = 0; i < NW; i++) w[i] = g[i];
+        if (Arith<POLICY>::modular) {
+            // unwrap the reference's mod-256 metrics around state 0 (spread < 128): U = 256 + m0 + (int8)(m - m0)
+            const int m0 = (int)(w[0] & 0xffu);
+#pragma unroll
+            for (int i = 0; i < NW; i++) {
+                const int lo = 256 + m0 + (int)(int8_t)((w[i] & 0xffu) - m0);
+                const int hi = 256 + m0 + (int)(int8_t)(((w[i] >> 16) & 0xffu) - m0);
+                w[i] = pack2((uint32_t)lo, (uint32_t)hi);
+            }
+        }
+    }
+
+    const unsigned char* sp = a.syms + (size_t)f * a.sym_stride;
+    unsigned long long* drow = a.dec + (size_t)a.step0 * a.n_frames + f;
+    const size_t dstride = (size_t)a.n_frames;
+
+    const int periods = a.nsteps / NB;
+    PeriodBuf<R> cur, nxt;
+    if (periods > 0) cur.load(sp);
+#pragma unroll 1
+    for (int pd = 0; pd < periods; pd++) {
+        if (pd + 1 < periods) nxt.load(sp + (size_t)(pd + 1) * NB * R);
+        unsigned long long d0, d1, d2, d3, d4, d5;
+        run_step<POLICY, CODE, 0>(w, cur, a, off, &d0);
+        run_step<POLICY, CODE, 1>(w, cur, a, off, &d1);
+        run_step<POLICY, CODE, 2>(w, cur, a, off, &d2);
+        run_step<POLICY, CODE, 3>(w, cur, a, off, &d3);
+        run_step<POLICY, CODE, 4>(w, cur, a, off, &d4);
+        run_step<POLICY, CODE, 5>(w, cur, a, off, &d5);
+        drow[0] = d0; drow[dstride] = d1; drow[2 * dstride] = d2;
+        drow[3 * dstride] = d3; drow[4 * dstride] = d4; drow[5 * dstride] = d5;
+        drow += 6 * dstride;
+        cur = nxt;
+        // keep the 16-bit lanes from overflowing: every 64 periods rebase (uniform across the warp)
+        if ((pd & 63) == 63) {
+            if (Arith<POLICY>::modular) {
+                // subtract a multiple of 256 (keeps U mod 256): floor(min/256)*256 - 256
+                uint32_t mn = w[0];
+#pragma unroll
+                for (int i = 1; i < NW; i++) mn = __vminu2(mn, w[i]);
+                const uint32_t m = min(mn & 0xffffu, mn >> 16);
+                const uint32_t sub = (m & ~255u) >= 256u ? (m & ~255u) - 256u : 0u;
+#pragma unroll
+                for (int i = 0; i < NW; i++) w[i] -= sub * 0x10001u;
+            } else {
+#pragma unroll
+                for (int i = 0; i < NW; i++) w[i] -= off * 0x10001u;    // every lane >= off: no borrow
+                off = 0;
+            }
+        }
+    }
+
+    // ---- tail: fewer than 6 steps left ----
+    const int rem = a.nsteps - periods * NB;
+    if (rem > 0) {
+        PeriodBuf<R> tb;
+        const unsigned char* tp = sp + (size_t)periods * NB * R;
+#pragma unroll
+        for (int i = 0; i < PeriodBuf<R>::WORDS; i++) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if (i * 4 + b < rem * R) v |= (uint32_t)__ldg(tp + i * 4 + b) << (8 * b);
+            tb.w[i] = v;
+        }
+        unsigned long long d;
+        if (rem > 0) { run_step<POLICY, CODE, 0>(w, tb, a, off, &d); drow[0] = d; }
+        if (rem > 1) { run_step<POLICY, CODE, 1>(w, tb, a, off, &d); drow[dstride] = d; }
+        if (rem > 2) { run_step<POLICY, CODE, 2>(w, tb, a, off, &d); drow[2 * dstride] = d; }
+        if (rem > 3) { run_step<POLICY, CODE, 3>(w, tb, a, off, &d); drow[3 * dstride] = d; }
+        if (rem > 4) { run_step<POLICY, CODE, 4>(w, tb, a, off, &d); drow[4 * dstride] = d; }
+    }
+
+    // ---- store canonical metrics: logical state n sits at physical_of(rem, n) ----
+    uint32_t tmp[NW];
+#pragma unroll
+    for (int i = 0; i < NW; i++) tmp[i] = w[i];
+    uint16_t* gm = a.metrics + (size_t)f * S;
+    for (int n = 0; n < S; n++) {
+        const int q = physical_of(rem, n);
+        const uint32_t v = (tmp[q >> 1] >> ((q & 1) * 16)) & 0xffffu;
+        gm[n] = (uint16_t)(Arith<POLICY>::modular ? (v & 0xffu) : (v - off));
+    }
+}
+
+
+template <int POLICY, class CODE>
+static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
+    const int threads = 128;
+    const int blocks = (a.n_frames + threads - 1) / threads;
+    acs_k7_kernel<POLICY, CODE><<<blocks, threads, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+using CodeK7R2 = Code<2, 0x6d, 0x4f, 0, 0>;   // src/main.cpp:367 (Voyager)
+
+// index of the instantiation matching (policy, R, poly), or -1
+static int find_instance(const CodecParams& c) {
+    if (c.K != 7) return -1;
+    if (c.R == 2 && c.poly[0] == 0x6d && c.poly[1] == 0x4f) {
+        if (c.policy == P_KA9Q_U8_MOD) return 0;
+        if (c.policy == P_SPIRAL_R2) return 1;
+        if (c.policy == P_WY_U8) return 2;
+    }
+    return -1;
+}
+
+}  // namespace k7
+
+bool k7_supported(const CodecParams& c) {
+    if (k7::find_instance(c) < 0) return false;
+    // wy-u8: the offset representation needs headroom above the saturation point
+    if (c.policy == P_WY_U8 && (c.max_error > 255 || c.renorm_threshold > 255 || c.init_other > 255)) return false;
+    return true;
+}
+
+cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                          unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
+                          cudaStream_t st) {
+    if (n_frames <= 0 || nsteps <= 0) return cudaSuccess;
+    k7::K7Args a;
+    a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
+    a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
+    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
+    switch (k7::find_instance(c)) {
+    case 0: return k7::launch_one<P_KA9Q_U8_MOD, k7::CodeK7R2>(a, st);
+    case 1: return k7::launch_one<P_SPIRAL_R2, k7::CodeK7R2>(a, st);
+    case 2: return k7::launch_one<P_WY_U8, k7::CodeK7R2>(a, st);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace b200v

@@ -143,6 +143,7 @@ struct b200v_batch {
     void* d_dec = nullptr;       size_t dec_bytes = 0;
     uint16_t* d_metrics = nullptr;
     uint8_t* d_cw = nullptr;
+    uint8_t* d_row_phase = nullptr;   // K=7 register family: phase of the step that wrote each decision row
     int* d_results = nullptr;
     // lazily allocated staging for the host-pointer entry points
     void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
@@ -153,7 +154,7 @@ static void free_all(b200v_batch* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
-    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_cw); cudaFree(h->d_results);
+    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase);
     cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
@@ -223,8 +224,13 @@ static int create_impl(b200v_batch* h, int starting_state) {
     const GenericPlan plan = generic_plan(c);
     if (plan.smem_bytes > 227 * 1024)
         return fail(B200V_ERR_ARG, "K=%d needs %d bytes of shared memory per block", c.K, plan.smem_bytes);
-    h->variant = 1;
-    h->layout = DL_BALLOT_FRAME_MAJOR;
+    CUDA_TRY(cudaMalloc(&h->d_row_phase, (size_t)h->dec_rows));
+    CUDA_TRY(cudaMemsetAsync(h->d_row_phase, 0, (size_t)h->dec_rows, h->stream));
+    // the register-resident family exists for the polynomial sets it was instantiated for; both families
+    // use 8 bytes per (row, frame) for K=7, so they share the decision buffer
+    h->has_fast = k7_supported(c);
+    h->variant = h->has_fast ? 2 : 1;
+    h->layout = h->has_fast ? DL_K7_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
     return b200v_batch_init(h, starting_state);
 }
 
@@ -237,8 +243,10 @@ extern "C" int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream) {
 extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     if (variant == 0) variant = h->has_fast ? 2 : 1;
-    if (variant == 1) { h->variant = 1; return B200V_OK; }
-    if (variant == 2 && h->has_fast) { h->variant = 2; return B200V_OK; }
+    if (variant != h->variant && h->cursor != 0)
+        return fail(B200V_ERR_STATE, "the kernel family can only change right after init (decision layouts differ)");
+    if (variant == 1) { h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
+    if (variant == 2 && h->has_fast) { h->variant = 2; h->layout = DL_K7_INTERLEAVED; return B200V_OK; }
     return fail(B200V_ERR_ARG, "kernel family %d is not available for this instance", variant);
 }
 extern "C" int b200v_batch_get_variant(const b200v_batch* h) { return h ? h->variant : 0; }
@@ -267,7 +275,11 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
     CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
-    if (nsteps > 0) {
+    if (nsteps > 0 && h->variant == 2) {
+        CUDA_TRY(launch_acs_k7(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (unsigned long long*)h->d_dec,
+                               h->d_row_phase, h->d_metrics, h->n_frames, h->stream));
+        h->launches++;
+    } else if (nsteps > 0) {
         GenericArgs a{};
         a.c = c; a.syms = d_syms; a.sym_stride = frame_stride_bytes; a.nsteps = nsteps; a.step0 = h->cursor;
         a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
@@ -319,6 +331,7 @@ extern "C" int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t
     CUDA_TRY(cudaSetDevice(h->device));
     ChainbackArgs a{};
     a.c = c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
+    a.row_phase = h->d_row_phase;
     a.n_frames = h->n_frames; a.metrics = h->d_metrics; a.out = d_data; a.out_stride = frame_stride_bytes;
     a.nbits = nbits; a.endstate = endstate; a.results = h->d_results;
     CUDA_TRY(cudaEventRecord(h->ev_c0, h->stream));
@@ -397,6 +410,24 @@ extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, i
                 ballot_position((unsigned)n, w, b);
                 o[n >> 3] |= (uint8_t)(((r[w] >> b) & 1u) << (n & 7));
             }
+        }
+        return B200V_OK;
+    }
+    if (h->layout == DL_K7_INTERLEAVED) {
+        std::vector<unsigned long long> rows((size_t)nsteps);
+        std::vector<uint8_t> phase((size_t)nsteps);
+        const unsigned long long* src = (const unsigned long long*)h->d_dec + (size_t)step0 * h->n_frames + frame;
+        if (nsteps > 0) {
+            CUDA_TRY(cudaMemcpy2DAsync(rows.data(), 8, src, (size_t)h->n_frames * 8, 8, (size_t)nsteps,
+                                       cudaMemcpyDeviceToHost, h->stream));
+            CUDA_TRY(cudaMemcpyAsync(phase.data(), h->d_row_phase + step0, (size_t)nsteps, cudaMemcpyDeviceToHost,
+                                     h->stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        }
+        for (int t = 0; t < nsteps; t++) {
+            uint8_t* o = out + (size_t)t * nb;
+            for (int n = 0; n < S; n++)
+                o[n >> 3] |= (uint8_t)(((rows[t] >> k7::decision_bit_of(phase[t], n)) & 1ull) << (n & 7));
         }
         return B200V_OK;
     }

@@ -16,7 +16,7 @@ __global__ void chainback_kernel(const ChainbackArgs a) {
     const int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= a.n_frames) return;
     const int K = a.c.K;
-    const DecisionReader<LAYOUT> rd(a, f);
+    const DecisionReader<LAYOUT> rd(a, f);   // frame-major layouts only
     uint8_t* out = a.out + (size_t)f * a.out_stride;
 
     if (a.c.policy == P_KA9Q_S16_224) {
@@ -52,6 +52,40 @@ __global__ void chainback_kernel(const ChainbackArgs a) {
     }
 }
 
+// K=7 register-resident family. The decision word of a row does not depend on the traced state, so the
+// loads are issued CHUNK rows ahead of the dependent bit extraction: the kernel streams the decision buffer
+// at memory bandwidth instead of paying one DRAM latency per decoded bit.
+__global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a) {
+    __shared__ uint8_t tab[k7::NB * k7::S];
+    fill_k7_table(tab);
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= a.n_frames) return;
+    constexpr int K = 7, CHUNK = 16;
+    const DecisionReader<DL_K7_INTERLEAVED> rd(a, f, tab);
+    uint8_t* out = a.out + (size_t)f * a.out_stride;
+    // K-1 = 6 < 8: the register keeps the state in its top 6 bits of a byte (ADDSHIFT = 2)
+    unsigned reg = (a.endstate % 64u) << 2;
+    if (a.results) a.results[f] = 0;
+    unsigned n = a.nbits;
+    while (n > 0) {
+        const unsigned cnt = n < (unsigned)CHUNK ? n : (unsigned)CHUNK;
+        unsigned long long wbuf[CHUNK];
+#pragma unroll
+        for (int i = 0; i < CHUNK; i++)
+            if ((unsigned)i < cnt) wbuf[i] = rd.load(n - 1 - i + (K - 1));
+#pragma unroll
+        for (int i = 0; i < CHUNK; i++) {
+            if ((unsigned)i < cnt) {
+                const unsigned row = n - 1 - i + (K - 1);
+                const unsigned k = rd.bit_of(wbuf[i], row, reg >> 2);
+                reg = (reg >> 1) | (k << 7);
+                if (((n - 1 - i) & 7u) == 0) out[(n - 1 - i) >> 3] = (uint8_t)reg;
+            }
+        }
+        n -= cnt;
+    }
+}
+
 }  // namespace
 
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
@@ -60,6 +94,7 @@ cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
     const int blocks = (a.n_frames + threads - 1) / threads;
     switch (a.layout) {
     case DL_BALLOT_FRAME_MAJOR: chainback_kernel<DL_BALLOT_FRAME_MAJOR><<<blocks, threads, 0, st>>>(a); break;
+    case DL_K7_INTERLEAVED: chainback_k7_kernel<<<blocks, threads, 0, st>>>(a); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -2,6 +2,7 @@
 // kernels (and the host-side canonicaliser in api.cu) find the bit of a given state.
 #pragma once
 #include "kernels.h"
+#include "acs_k7.cuh"
 
 namespace b200v {
 
@@ -26,5 +27,29 @@ template <> struct DecisionReader<DL_BALLOT_FRAME_MAJOR> {
         return (__ldg(base + (size_t)row * row_words + w) >> b) & 1u;
     }
 };
+
+
+// register-resident K=7 family: one u64 per (row, frame), frame-interleaved; the bit of state n depends on the
+// phase of the step that wrote the row (acs_k7.cuh: decision_bit_of). `tab` is a [6][64] byte table in shared
+// memory filled by fill_k7_table().
+template <> struct DecisionReader<DL_K7_INTERLEAVED> {
+    const unsigned long long* base;   // + frame
+    size_t stride;                    // n_frames
+    const uint8_t* row_phase;
+    const uint8_t* tab;
+    __device__ DecisionReader(const ChainbackArgs& a, int frame, const uint8_t* table)
+        : base((const unsigned long long*)a.dec + frame), stride((size_t)a.n_frames), row_phase(a.row_phase),
+          tab(table) {}
+    __device__ __forceinline__ unsigned long long load(unsigned row) const { return __ldg(base + (size_t)row * stride); }
+    __device__ __forceinline__ unsigned bit_of(unsigned long long word, unsigned row, unsigned state) const {
+        return (unsigned)(word >> tab[row_phase[row] * k7::S + state]) & 1u;
+    }
+};
+
+__device__ __forceinline__ void fill_k7_table(uint8_t* tab) {
+    for (int i = threadIdx.x; i < k7::NB * k7::S; i += blockDim.x)
+        tab[i] = (uint8_t)k7::decision_bit_of(i / k7::S, i % k7::S);
+    __syncthreads();
+}
 
 }  // namespace b200v

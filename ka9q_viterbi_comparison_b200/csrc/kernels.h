@@ -28,12 +28,19 @@ cudaError_t launch_acs_generic(const GenericArgs& a, cudaStream_t st);
 cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecParams& c, int starting_state,
                                 cudaStream_t st);
 
+// ---- register-resident K=7 kernels (acs_k7.cu): decisions as one u64 per (row, frame), dec[row*n_frames+f] ----
+bool k7_supported(const CodecParams& c);
+cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                          unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
+                          cudaStream_t st);
+
 // ---- chainback (chainback.cu) ---------------------------------------------------------------------
 struct ChainbackArgs {
     CodecParams c;
     int layout;                 // DecisionLayout
     const void* dec;
     int dec_rows, row_words;    // DL_BALLOT_FRAME_MAJOR geometry
+    const uint8_t* row_phase;   // DL_K7_INTERLEAVED: phase of the step that wrote each row
     int n_frames;
     const uint16_t* metrics;    // for the KA9Q615 return value
     uint8_t* out;               // device; frame f at out + f*out_stride

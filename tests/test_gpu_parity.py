@@ -44,6 +44,7 @@ def make_batch(c, n_frames, nbytes, sigma, seed):
 def variants(dec):
     """Kernel families available for this instance (1 = generic always; 2 = specialised when present)."""
     out = [1]
+    dec.reset()
     try:
         dec.set_variant(2)
         out.append(2)
@@ -64,6 +65,7 @@ def test_matches_golden_reference_vectors(name):
         nbits = T - (K - 1)
         with kv.BatchDecoder(codec, T, 1, K=K, R=R) as dec:
             for v in variants(dec):
+                dec.reset()
                 dec.set_variant(v)
                 dec.reset()
                 dec.update(syms)
@@ -85,6 +87,7 @@ def test_batch_matches_oracle(name, sigma):
     data, syms = make_batch(c, n_frames, nbytes, sigma, seed=0x5EED)
     with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
         for v in variants(dec):
+            dec.reset()
             dec.set_variant(v)
             out = dec.decode(syms, nbytes * 8)
             rcs = dec.chainback_results()
@@ -113,6 +116,7 @@ def test_streaming_update_matches_oracle(name):
     data, syms = make_batch(c, n_frames, nbytes, 0.8, seed=11)
     with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
         for v in variants(dec):
+            dec.reset()
             dec.set_variant(v)
             dec.reset()
             pos = 0
@@ -165,6 +169,7 @@ def test_extreme_symbol_patterns():
         nbits = T - (K - 1)
         with kv.BatchDecoder(codec, T, pats.shape[0], K=K, R=R) as dec:
             for v in variants(dec):
+                dec.reset()
                 dec.set_variant(v)
                 dec.reset()
                 dec.update(pats)
