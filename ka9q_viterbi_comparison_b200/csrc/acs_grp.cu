@@ -1,0 +1,462 @@
+// acs_grp.cu -- "group" add-compare-select kernels for K = 9 and K = 15: TPF = 2^(K-7) threads per frame, each
+// holding 64 path metrics in 32 registers of u16x2 (index algebra: acs_grp.cuh). Five trellis steps run
+// entirely in registers (in-place rotating layout, static register indices); every fifth step the threads of
+// a frame exchange metrics through shared memory (one transposition, swizzled, conflict-free for K=15).
+//   K=15: 256 threads = one frame per block;  K=9: 4 threads per frame, 32 frames per 128-thread block.
+// Per pair of registers (2 butterflies, 4 new states): 1 LDS.64 of the packed branch metrics
+// {(bm[c], bm[c^D]), (cm[c], cm[c^D])} from a per-step table in shared memory (indexed by the static code word
+// of the register pair XOR the thread's own code-word contribution), 4 VIADDMNMX.U16x2 (saturating add as
+// add+min), 2 VIMNMX.U16x2 with predicate outputs (compare-select + both decisions), 4 predicated ORs.
+//
+// Takes the role of update_viterbi615_blk_sse2 (ka9q_libfec_port/viterbi615_sse2.cpp:104-191),
+// update_spiral29/49/615 (spiral/spiral29.cpp, spiral49.cpp, spiral615.cpp:130-415) and
+// ViterbiDecoder_SSE_u8<K,R>::update (viterbi/x86/viterbi_decoder_sse_u8.h:45-154) for a batch of frames.
+//
+// Bit-exactness: lanes hold w = tb - base, tb = the reference's metric (s16 metrics biased by +32768 so that
+// signed min/saturation become unsigned), base = a per-frame integer every thread of the frame tracks.
+//  * saturation at TOP (255 / 65535) is the clamp operand TOP - base of VIADDMNMX (exact whenever it can bind);
+//  * "if new[0] crosses the threshold subtract the minimum of all states" (viterbi615_sse2.cpp:160-183,
+//    spiral615.cpp:31-40, sse_u8.h:127-154) becomes base = -min(w): the frame-wide minimum is reduced after
+//    EVERY step (REDUX + one barrier for K=15, two shuffles for K=9), so the trigger is evaluated at exactly
+//    the step the reference evaluates it;
+//  * lanes are kept inside 16 bits by rebasing (w -= min, base += min) whenever min(w) > 16384.
+#include "kernels.h"
+#include "acs_grp.cuh"
+#include "dpx.cuh"
+#include "policy.cuh"
+
+namespace b200v {
+namespace grp {
+
+template <int K_, int R_, int P0, int P1, int P2, int P3, int P4, int P5>
+struct Code {
+    static constexpr int K = K_, R = R_;
+    __host__ __device__ static constexpr unsigned poly(int i) {
+        return (unsigned)(i == 0 ? P0 : i == 1 ? P1 : i == 2 ? P2 : i == 3 ? P3 : i == 4 ? P4 : P5);
+    }
+    // code word of the butterfly whose doubled index 2j is x: bit i = parity(x & poly_i)
+    __host__ __device__ static constexpr unsigned cw2(unsigned x) {
+        unsigned c = 0;
+        for (int i = 0; i < R; i++) c |= (unsigned)k7::parity_of(x & poly(i)) << i;
+        return c;
+    }
+};
+
+template <int POLICY, class CODE>
+struct Cfg {
+    static constexpr int K = CODE::K, R = CODE::R, NB = K - 1, NXB = NB - NL, S = 1 << NB, NCW = 1 << R;
+    static constexpr int TPF = 1 << (NXB - 1);                  // threads per frame
+    static constexpr int FPB = TPF >= 32 ? 1 : 128 / TPF;       // frames per block
+    static constexpr int THREADS = TPF * FPB;
+    static constexpr int MET_STRIDE = S * 2 + (TPF < 32 ? 16 : 0);   // bytes of exchange buffer per frame
+    static constexpr int SUBTAB = NCW * 8;                      // one step's table: NCW x {W, Wc}
+    static constexpr int TAB_BYTES = 2 * NL * SUBTAB;           // two groups (double buffer) x five steps
+    static constexpr int RED_WORDS = 2 * 16;                    // block reduction scratch (TPF >= 32)
+    static constexpr int SMEM = FPB * TAB_BYTES + FPB * MET_STRIDE + RED_WORDS * 4;
+    static constexpr bool s16 = (POLICY == P_KA9Q_S16_615);
+    static constexpr bool strict = PolicyTraits<POLICY>::renorm_strict;
+    static constexpr int TOP = (s16 || POLICY == P_WY_U16) ? 65535 : 255;
+    static_assert(NXB >= 3, "at least 4 threads per frame");
+    static_assert(TPF <= 4 || NXB + 1 >= 10, "exchange swizzle is written for K=9 and K=15");
+};
+
+struct GrpArgs {
+    const unsigned char* syms; size_t sym_stride;
+    int nsteps, step0;
+    unsigned long long* dec;       // dec[((step0 + t) * n_frames + frame) * TPF + tx]
+    uint8_t* row_phase;
+    uint16_t* metrics;             // canonical [n_frames][S]
+    int n_frames;
+    int C, thr, soft_hi, soft_lo;
+};
+
+// scalar branch metric / complement of code word cw for one step's symbols (same formulas as policy.cuh)
+template <int POLICY, int R>
+__device__ __forceinline__ void bm_eval(unsigned cw, const int* sym, const GrpArgs& a, uint32_t& bm, uint32_t& cm) {
+    int v;
+    if (POLICY == P_WY_U8) {
+        int tot = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int bt = ((cw >> i) & 1u) ? a.soft_hi : a.soft_lo;
+            tot = min(tot + abs(clamp_i(bt - sym[i], -128, 127)), 255);
+        }
+        v = tot;
+    } else if (POLICY == P_KA9Q_S16_615) {
+        int s = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) s += ((cw >> i) & 1u) ? (sym[i] ^ 255) : sym[i];
+        v = s;
+    } else if (POLICY == P_SPIRAL_R2) {
+        const int x0 = (cw & 1u) ? (sym[0] ^ 255) : sym[0];
+        const int x1 = (cw & 2u) ? (sym[1] ^ 255) : sym[1];
+        v = (((x0 + x1 + 1) >> 1) >> 2) & 63;
+    } else {   // P_SPIRAL_R4, P_SPIRAL_615
+        int s = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int x = ((cw >> i) & 1u) ? (sym[i] ^ 255) : sym[i];
+            s = min(s + ((x >> 2) & 63), 255);
+        }
+        v = (s >> 2) & 63;
+    }
+    bm = (uint32_t)v;
+    cm = (uint32_t)max(a.C - v, 0);
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void lds64(uint32_t addr, uint32_t& x, uint32_t& y) {
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(y) : "r"(addr));
+}
+__device__ __forceinline__ void sts64(uint32_t addr, uint32_t x, uint32_t y) {
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// 16-byte-chunk swizzle of the exchange buffer: chunk index ^= low bits of the 128-byte line index
+__device__ __forceinline__ uint32_t swz(uint32_t byte_off) { return byte_off ^ (((byte_off >> 7) & 7u) << 4); }
+
+// ---- frame-wide minimum (and state 0's metric) after a step ----------------------------------------------
+// lm: the thread's minimum over its 64 lanes (u16 value); w0: the thread's register 0 (state 0 lives in lane 0
+// of register 0 of thread tx = 0 in every phase). TPF >= 32: one REDUX per warp, one barrier per step, scratch
+// double-buffered by `rpar` so that a single barrier per step suffices. TPF < 32: shuffles inside the warp.
+template <class CF>
+__device__ __forceinline__ void frame_min(uint32_t lm, uint32_t w0, uint32_t* s_red, int& rpar, int tid,
+                                          uint32_t& gmin, uint32_t& g0) {
+    if (CF::TPF >= 32) {
+        constexpr int NWARP = CF::TPF / 32;
+        const uint32_t wm = __reduce_min_sync(0xffffffffu, lm);
+        uint32_t* r = s_red + rpar * 16;
+        if ((tid & 31) == 0) r[tid >> 5] = wm;
+        if (tid == 0) r[NWARP] = w0 & 0xffffu;
+        __syncthreads();
+        uint32_t m = r[0];
+#pragma unroll
+        for (int i = 1; i < NWARP; i++) m = min(m, r[i]);
+        gmin = m;
+        g0 = r[NWARP];
+        rpar ^= 1;
+    } else {
+#pragma unroll
+        for (int o = 1; o < CF::TPF; o <<= 1) lm = min(lm, __shfl_xor_sync(0xffffffffu, lm, o));
+        gmin = lm;
+        g0 = __shfl_sync(0xffffffffu, w0, (tid & 31) & ~(CF::TPF - 1)) & 0xffffu;
+    }
+}
+
+__device__ __forceinline__ uint32_t local_min(const uint32_t (&w)[NREG]) {
+    uint32_t mn = __vimin3_u16x2(w[0], w[1], w[2]);
+#pragma unroll
+    for (int i = 3; i + 1 < NREG; i += 2) mn = __vimin3_u16x2(mn, w[i], w[i + 1]);
+    mn = __vminu2(mn, w[NREG - 1]);
+    return min(mn & 0xffffu, mn >> 16);
+}
+
+// per-frame running state every thread of the frame keeps identically
+struct FrameState {
+    int base;          // tb = w + base
+    uint32_t clamp;    // packed clamp operand of the saturating adds
+};
+
+template <int POLICY, class CF>
+__device__ __forceinline__ void set_clamp(FrameState& fs, int bm_max) {
+    const int c = min(CF::TOP - fs.base, 65535 - bm_max);
+    fs.clamp = (uint32_t)c * 0x10001u;
+}
+
+// trigger + rebase after a step, given the frame-wide minimum and w[0] of state 0
+template <int POLICY, class CF>
+__device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint32_t gmin, uint32_t g0, const GrpArgs& a) {
+    const int tb0 = (int)g0 + fs.base;
+    const int thr = a.thr + (CF::s16 ? 32768 : 0);
+    const bool need = CF::strict ? (tb0 > thr) : (tb0 >= thr);
+    if (need) fs.base = -(int)gmin;
+    if (gmin > 16384u) {       // uniform over the frame
+        const uint32_t sub = gmin * 0x10001u;
+#pragma unroll
+        for (int i = 0; i < NREG; i++) w[i] -= sub;      // every lane >= gmin: no borrow between lanes
+        fs.base += (int)gmin;
+    }
+    set_clamp<POLICY, CF>(fs, CF::TOP == 255 ? 255 : a.C);
+}
+
+// ---- butterflies of one step in phase P -------------------------------------------------------------------
+template <int POLICY, class CODE, int P, int KK>
+struct PairLoop {
+    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], uint32_t A, uint32_t clamp, uint32_t& acc0,
+                                               uint32_t& acc1) {
+        constexpr int NXB = CODE::K - 1 - NL;
+        constexpr int XB = NL - 1 - P;
+        constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
+        constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
+        uint32_t W, Wc;
+        lds64(A ^ (c << 3), W, Wc);
+        const uint32_t m0 = __viaddmin_u16x2(w[iA], W, clamp), m1 = __viaddmin_u16x2(w[iB], Wc, clamp);
+        const uint32_t m2 = __viaddmin_u16x2(w[iA], Wc, clamp), m3 = __viaddmin_u16x2(w[iB], W, clamp);
+        // decision = (min == hi path): tie -> 1 (viterbi615_sse2.cpp:145-148, spiral615.cpp:247-250, sse_u8.h:111-114)
+        w[iA] = min_acc<KK, 16 + KK, false>(m1, m0, acc0);
+        w[iB] = min_acc<KK, 16 + KK, false>(m3, m2, acc1);
+        PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, acc0, acc1);
+    }
+};
+template <int POLICY, class CODE, int P>
+struct PairLoop<POLICY, CODE, P, 16> {
+    __device__ __forceinline__ static void run(uint32_t (&)[NREG], uint32_t, uint32_t, uint32_t&, uint32_t&) {}
+};
+
+// exchange after a whole group: phase-5 layout (register q, lane, tx) = state (2tx+lane)*32 + q  ->  shared
+template <class CF>
+__device__ __forceinline__ void exchange_store(const uint32_t (&w)[NREG], uint32_t met_addr, int tx) {
+    const uint32_t line = met_addr + (uint32_t)tx * 128u;
+    const uint32_t key = ((uint32_t)tx & 7u) << 4;
+#pragma unroll
+    for (int ch = 0; ch < 8; ch++) {
+        const int q0 = (ch & 3) * 8;
+        const uint32_t sel = (ch < 4) ? 0x5410u : 0x7632u;     // lane 0 halves / lane 1 halves of (w[q], w[q+1])
+        sts128(line + (((uint32_t)ch << 4) ^ key),
+               __byte_perm(w[q0], w[q0 + 1], sel), __byte_perm(w[q0 + 2], w[q0 + 3], sel),
+               __byte_perm(w[q0 + 4], w[q0 + 5], sel), __byte_perm(w[q0 + 6], w[q0 + 7], sel));
+    }
+}
+// shared -> phase-0 layout: register q = states (q * 2^NXB + 2tx, +1)
+template <class CF>
+__device__ __forceinline__ void exchange_load(uint32_t (&w)[NREG], uint32_t met_addr, int tx) {
+    if (CF::NXB + 1 >= 10) {
+        const uint32_t t = met_addr + swz(4u * (uint32_t)tx);
+#pragma unroll
+        for (int q = 0; q < NREG; q++) w[q] = lds32(t + ((uint32_t)q << (CF::NXB + 1)));
+    } else {
+        const uint32_t t = met_addr + 4u * (uint32_t)tx;
+#pragma unroll
+        for (int q = 0; q < NREG; q++) w[q] = lds32(t + swz((uint32_t)q << (CF::NXB + 1)));
+    }
+}
+
+// ---- branch-metric tables of one group of five steps ---------------------------------------------------
+// entry (s, c) = { pack(bm[c], bm[c ^ D_s]), pack(cm[c], cm[c ^ D_s]) }, D_s = code-word difference between the
+// two lanes of a register in phase s. One task computes bm of c and c ^ D_s once and writes both entries.
+template <int POLICY, class CODE, class CF>
+__device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx) {
+    constexpr int R = CF::R, HALF = CF::NCW / 2;
+    const uint32_t buf = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
+    for (int e = tx; e < NL * HALF; e += CF::TPF) {
+        const int s = e / HALF, idx = e - s * HALF;
+        const int t = g * NL + s;
+        if (t >= a.nsteps) break;
+        const unsigned D = CODE::cw2(1u << (s + 1));
+        unsigned c1, c2;
+        if (D) { c1 = (unsigned)k7::expand_bit(idx, 31 - __clz(D)); c2 = c1 ^ D; }
+        else { c1 = (unsigned)idx; c2 = (unsigned)(idx + HALF); }
+        int sym[R];
+        const unsigned char* p = sp + (size_t)t * R;
+#pragma unroll
+        for (int i = 0; i < R; i++) sym[i] = (POLICY == P_WY_U8) ? (int)(int8_t)__ldg(p + i) : (int)__ldg(p + i);
+        uint32_t b1, m1, b2, m2;
+        bm_eval<POLICY, R>(c1, sym, a, b1, m1);
+        bm_eval<POLICY, R>(c2, sym, a, b2, m2);
+        const uint32_t st = buf + (uint32_t)s * CF::SUBTAB;
+        if (D) {
+            sts64(st + c1 * 8, pack2(b1, b2), pack2(m1, m2));
+            sts64(st + c2 * 8, pack2(b2, b1), pack2(m2, m1));
+        } else {
+            sts64(st + c1 * 8, pack2(b1, b1), pack2(m1, m1));
+            sts64(st + c2 * 8, pack2(b2, b2), pack2(m2, m2));
+        }
+    }
+}
+
+// ---- one trellis step in phase P -------------------------------------------------------------------------
+// EXCH: this is the fifth step of a whole group: store the metrics for the exchange before the step's barrier
+// and reload them in the phase-0 layout after it.
+template <int POLICY, class CODE, class CF, int P, bool EXCH>
+__device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const GrpArgs& a, uint32_t sub_addr,
+                                     uint32_t cx8, unsigned long long* dec_out, bool live, uint32_t met_addr,
+                                     uint32_t* s_red, int& rpar, int tid, int tx) {
+    uint32_t acc0 = 0, acc1 = 0;
+    PairLoop<POLICY, CODE, P, 0>::run(w, sub_addr + cx8, fs.clamp, acc0, acc1);
+    if (live) *dec_out = (unsigned long long)acc0 | ((unsigned long long)acc1 << 32);
+    const uint32_t lm = local_min(w);
+    const uint32_t w0 = w[0];
+    if (EXCH) {
+        exchange_store<CF>(w, met_addr, tx);
+        if (CF::TPF < 32) __syncwarp();
+    }
+    uint32_t gmin, g0;
+    frame_min<CF>(lm, w0, s_red, rpar, tid, gmin, g0);
+    if (EXCH) exchange_load<CF>(w, met_addr, tx);
+    renorm<POLICY, CF>(w, fs, gmin, g0, a);
+}
+
+template <int POLICY, class CODE>
+__global__ void __launch_bounds__((Cfg<POLICY, CODE>::THREADS), (Cfg<POLICY, CODE>::TPF >= 32 ? 3 : 4))
+acs_grp_kernel(const GrpArgs a) {
+    using CF = Cfg<POLICY, CODE>;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int tid = threadIdx.x;
+    const int fl = tid / CF::TPF, tx = tid % CF::TPF;
+    const int frame_raw = blockIdx.x * CF::FPB + fl;
+    const bool live = frame_raw < a.n_frames;
+    const int frame = live ? frame_raw : a.n_frames - 1;
+
+    const uint32_t tab_addr = smem_u32(smem) + (uint32_t)fl * CF::TAB_BYTES;
+    unsigned char* met_ptr = smem + CF::FPB * CF::TAB_BYTES + (size_t)fl * CF::MET_STRIDE;
+    const uint32_t met_addr = smem_u32(met_ptr);
+    uint32_t* s_red = reinterpret_cast<uint32_t*>(smem + CF::FPB * CF::TAB_BYTES + CF::FPB * CF::MET_STRIDE);
+    int rpar = 0;
+
+    if (blockIdx.x == 0)
+        for (int t = tid; t < a.nsteps; t += blockDim.x) a.row_phase[a.step0 + t] = (uint8_t)(t % NL);
+
+    // ---- canonical metrics -> phase-0 layout: register q = states (q * 2^NXB + 2tx, +1) ----
+    uint32_t w[NREG];
+    uint16_t* gm = a.metrics + (size_t)frame * CF::S;
+    {
+        const uint32_t* g32 = reinterpret_cast<const uint32_t*>(gm);
+#pragma unroll
+        for (int q = 0; q < NREG; q++) {
+            w[q] = g32[q * CF::TPF + tx];
+            if (CF::s16) w[q] ^= 0x80008000u;          // s16 -> biased u16
+        }
+    }
+    FrameState fs;
+    fs.base = 0;
+    {   // bring the lanes down to the bottom of the 16-bit window
+        uint32_t gmin, g0;
+        frame_min<CF>(local_min(w), w[0], s_red, rpar, tid, gmin, g0);
+        const uint32_t sub = gmin * 0x10001u;
+#pragma unroll
+        for (int i = 0; i < NREG; i++) w[i] -= sub;
+        fs.base = (int)gmin;
+        set_clamp<POLICY, CF>(fs, CF::TOP == 255 ? 255 : a.C);
+    }
+
+    // the thread's own contribution to the code word of its butterflies, per phase (byte offset into a table)
+    uint32_t cx8[NL];
+#pragma unroll
+    for (int p = 0; p < NL; p++) {
+        unsigned c = 0;
+#pragma unroll
+        for (int i = 0; i < CF::R; i++) c |= (unsigned)(__popc(((unsigned)tx << (p + 2)) & CODE::poly(i)) & 1) << i;
+        cx8[p] = c << 3;
+    }
+
+    const unsigned char* sp = a.syms + (size_t)frame * a.sym_stride;
+    const size_t dstride = (size_t)a.n_frames * CF::TPF;
+    unsigned long long* drow = a.dec + ((size_t)a.step0 * a.n_frames + frame) * CF::TPF + tx;
+
+    const int ngroups = (a.nsteps + NL - 1) / NL;
+    if (ngroups > 0) fill_tables<POLICY, CODE, CF>(a, sp, 0, tab_addr, tx);
+    if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
+
+#pragma unroll 1
+    for (int g = 0; g < ngroups; g++) {
+        const int nsub = min(NL, a.nsteps - g * NL);
+        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx);
+        const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
+        step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
+        if (nsub > 1) step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);
+        if (nsub > 2) step<POLICY, CODE, CF, 2, false>(w, fs, a, gt + 2 * CF::SUBTAB, cx8[2], drow + 2 * dstride, live, met_addr, s_red, rpar, tid, tx);
+        if (nsub > 3) step<POLICY, CODE, CF, 3, false>(w, fs, a, gt + 3 * CF::SUBTAB, cx8[3], drow + 3 * dstride, live, met_addr, s_red, rpar, tid, tx);
+        if (nsub > 4) step<POLICY, CODE, CF, 4, true>(w, fs, a, gt + 4 * CF::SUBTAB, cx8[4], drow + 4 * dstride, live, met_addr, s_red, rpar, tid, tx);
+        drow += NL * dstride;
+    }
+
+    // ---- registers (phase pf layout) -> canonical metrics, through shared memory ----
+    const int pf = a.nsteps % NL;
+    if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
+#pragma unroll
+    for (int q = 0; q < NREG; q++)
+        asm volatile("st.shared.u32 [%0], %1;" :: "r"(met_addr + (uint32_t)(q * CF::TPF + tx) * 4u), "r"(w[q]) : "memory");
+    if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
+    if (live) {
+        const uint16_t* raw = reinterpret_cast<const uint16_t*>(met_ptr);
+        for (unsigned n = (unsigned)tx; n < (unsigned)CF::S; n += CF::TPF) {
+            int q;
+            unsigned xx;
+            locate_state(CF::NXB, pf, n, q, xx);
+            const int tb = (int)raw[(q * CF::TPF + (int)(xx >> 1)) * 2 + (int)(xx & 1u)] + fs.base;
+            gm[n] = (uint16_t)(CF::s16 ? (tb ^ 0x8000) : tb);
+        }
+    }
+}
+
+template <int POLICY, class CODE>
+static cudaError_t launch_one(const GrpArgs& a, cudaStream_t st) {
+    using CF = Cfg<POLICY, CODE>;
+    auto k = acs_grp_kernel<POLICY, CODE>;
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SMEM);
+    if (e != cudaSuccess) return e;
+    const int blocks = (a.n_frames + CF::FPB - 1) / CF::FPB;
+    k<<<blocks, CF::THREADS, CF::SMEM, st>>>(a);
+    return cudaGetLastError();
+}
+
+using CodeK9R2 = Code<9, 2, 0x1af, 0x11d, 0, 0, 0, 0>;                                   // src/main.cpp:386
+using CodeK9R4 = Code<9, 4, 501, 441, 331, 315, 0, 0>;                                   // src/main.cpp:396
+using CodeK15R6 = Code<15, 6, 042631, 047245, 056507, 073363, 077267, 064537>;           // src/main.cpp:405
+
+template <class CODE>
+static bool same_code(const CodecParams& c) {
+    if (c.K != CODE::K || c.R != CODE::R) return false;
+    for (int i = 0; i < CODE::R; i++)
+        if (c.poly[i] != (int)CODE::poly(i)) return false;
+    return true;
+}
+
+enum Instance { I_NONE = -1, I_KA9Q615, I_SPIRAL615, I_WY8_K15R6, I_SPIRAL29, I_WY8_K9R2, I_SPIRAL49, I_WY8_K9R4 };
+
+static int find_instance(const CodecParams& c) {
+    if (same_code<CodeK15R6>(c)) {
+        if (c.policy == P_KA9Q_S16_615) return I_KA9Q615;
+        if (c.policy == P_SPIRAL_615) return I_SPIRAL615;
+        if (c.policy == P_WY_U8) return I_WY8_K15R6;
+    } else if (same_code<CodeK9R2>(c)) {
+        if (c.policy == P_SPIRAL_R2) return I_SPIRAL29;
+        if (c.policy == P_WY_U8) return I_WY8_K9R2;
+    } else if (same_code<CodeK9R4>(c)) {
+        if (c.policy == P_SPIRAL_R4) return I_SPIRAL49;
+        if (c.policy == P_WY_U8) return I_WY8_K9R4;
+    }
+    return I_NONE;
+}
+
+}  // namespace grp
+
+bool grp_supported(const CodecParams& c) {
+    if (grp::find_instance(c) < 0) return false;
+    // wy-u8: the clamp arithmetic assumes the reference's u8 ranges
+    if (c.policy == P_WY_U8 && (c.max_error > 255 || c.renorm_threshold > 255 || c.init_other > 255 ||
+                                c.init_start > 255 || c.max_error < 0 || c.init_other < 0 || c.init_start < 0))
+        return false;
+    return true;
+}
+
+int grp_threads_per_frame(const CodecParams& c) { return 1 << (c.K - 1 - grp::NL - 1); }
+
+cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
+                           cudaStream_t st) {
+    if (n_frames <= 0 || nsteps <= 0) return cudaSuccess;
+    grp::GrpArgs a;
+    a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
+    a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
+    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
+    switch (grp::find_instance(c)) {
+    case grp::I_KA9Q615: return grp::launch_one<P_KA9Q_S16_615, grp::CodeK15R6>(a, st);
+    case grp::I_SPIRAL615: return grp::launch_one<P_SPIRAL_615, grp::CodeK15R6>(a, st);
+    case grp::I_WY8_K15R6: return grp::launch_one<P_WY_U8, grp::CodeK15R6>(a, st);
+    case grp::I_SPIRAL29: return grp::launch_one<P_SPIRAL_R2, grp::CodeK9R2>(a, st);
+    case grp::I_WY8_K9R2: return grp::launch_one<P_WY_U8, grp::CodeK9R2>(a, st);
+    case grp::I_SPIRAL49: return grp::launch_one<P_SPIRAL_R4, grp::CodeK9R4>(a, st);
+    case grp::I_WY8_K9R4: return grp::launch_one<P_WY_U8, grp::CodeK9R4>(a, st);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace b200v

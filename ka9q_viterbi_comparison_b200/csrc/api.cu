@@ -3,6 +3,7 @@
 #include "../../include/b200_viterbi.h"
 #include "kernels.h"
 #include "decision_layout.cuh"
+#include "acs_grp.cuh"
 
 #include <cstdarg>
 #include <cstdio>
@@ -135,6 +136,7 @@ struct b200v_batch {
     int variant = 1;             // kernel family in use (1 generic, 2 register-resident)
     int layout = DL_BALLOT_FRAME_MAJOR;
     bool has_fast = false;
+    int fast_layout = DL_BALLOT_FRAME_MAJOR;   // decision layout of the specialised family, if any
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev_u0 = nullptr, ev_u1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
     bool timed_update = false, timed_chainback = false;
@@ -228,9 +230,10 @@ static int create_impl(b200v_batch* h, int starting_state) {
     CUDA_TRY(cudaMemsetAsync(h->d_row_phase, 0, (size_t)h->dec_rows, h->stream));
     // the register-resident family exists for the polynomial sets it was instantiated for; both families
     // use 8 bytes per (row, frame) for K=7, so they share the decision buffer
-    h->has_fast = k7_supported(c);
+    h->fast_layout = k7_supported(c) ? DL_K7_INTERLEAVED : grp_supported(c) ? DL_GRP_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
+    h->has_fast = h->fast_layout != DL_BALLOT_FRAME_MAJOR;
     h->variant = h->has_fast ? 2 : 1;
-    h->layout = h->has_fast ? DL_K7_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
+    h->layout = h->fast_layout;
     return b200v_batch_init(h, starting_state);
 }
 
@@ -246,7 +249,7 @@ extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
     if (variant != h->variant && h->cursor != 0)
         return fail(B200V_ERR_STATE, "the kernel family can only change right after init (decision layouts differ)");
     if (variant == 1) { h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
-    if (variant == 2 && h->has_fast) { h->variant = 2; h->layout = DL_K7_INTERLEAVED; return B200V_OK; }
+    if (variant == 2 && h->has_fast) { h->variant = 2; h->layout = h->fast_layout; return B200V_OK; }
     return fail(B200V_ERR_ARG, "kernel family %d is not available for this instance", variant);
 }
 extern "C" int b200v_batch_get_variant(const b200v_batch* h) { return h ? h->variant : 0; }
@@ -275,7 +278,11 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
     CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
-    if (nsteps > 0 && h->variant == 2) {
+    if (nsteps > 0 && h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
+        CUDA_TRY(launch_acs_grp(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (unsigned long long*)h->d_dec,
+                                h->d_row_phase, h->d_metrics, h->n_frames, h->stream));
+        h->launches++;
+    } else if (nsteps > 0 && h->variant == 2) {
         CUDA_TRY(launch_acs_k7(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (unsigned long long*)h->d_dec,
                                h->d_row_phase, h->d_metrics, h->n_frames, h->stream));
         h->launches++;
@@ -428,6 +435,28 @@ extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, i
             uint8_t* o = out + (size_t)t * nb;
             for (int n = 0; n < S; n++)
                 o[n >> 3] |= (uint8_t)(((rows[t] >> k7::decision_bit_of(phase[t], n)) & 1ull) << (n & 7));
+        }
+        return B200V_OK;
+    }
+    if (h->layout == DL_GRP_INTERLEAVED) {
+        const int tpf = grp_threads_per_frame(h->c), nxb = h->c.K - 1 - grp::NL;
+        std::vector<unsigned long long> rows((size_t)nsteps * tpf);
+        std::vector<uint8_t> phase((size_t)nsteps);
+        const unsigned long long* src = (const unsigned long long*)h->d_dec + ((size_t)step0 * h->n_frames + frame) * tpf;
+        if (nsteps > 0) {
+            CUDA_TRY(cudaMemcpy2DAsync(rows.data(), (size_t)tpf * 8, src, (size_t)h->n_frames * tpf * 8, (size_t)tpf * 8,
+                                       (size_t)nsteps, cudaMemcpyDeviceToHost, h->stream));
+            CUDA_TRY(cudaMemcpyAsync(phase.data(), h->d_row_phase + step0, (size_t)nsteps, cudaMemcpyDeviceToHost,
+                                     h->stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        }
+        for (int t = 0; t < nsteps; t++) {
+            uint8_t* o = out + (size_t)t * nb;
+            for (int n = 0; n < S; n++) {
+                unsigned tx, b;
+                grp::decision_pos(nxb, phase[t], (unsigned)n, tx, b);
+                o[n >> 3] |= (uint8_t)(((rows[(size_t)t * tpf + tx] >> b) & 1ull) << (n & 7));
+            }
         }
         return B200V_OK;
     }

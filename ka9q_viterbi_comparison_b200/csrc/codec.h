@@ -40,6 +40,9 @@ enum DecisionLayout : int {
     // register-resident K=7 kernel: one u64 per (step, frame), frame-interleaved: dec[step][frame];
     // bit positions given by a per-phase permutation table (see acs_k7.cuh)
     DL_K7_INTERLEAVED = 1,
+    // group family (K=9, K=15; acs_grp.cuh): one u64 per (step, frame, thread-of-frame), frame-interleaved:
+    // dec[(step*n_frames + frame)*TPF + tx]; bit positions depend on the phase (step mod 5) of the row
+    DL_GRP_INTERLEAVED = 2,
 };
 
 static inline bool policy_is_spiral(int p) { return p == P_SPIRAL_R2 || p == P_SPIRAL_R4 || p == P_SPIRAL_615; }

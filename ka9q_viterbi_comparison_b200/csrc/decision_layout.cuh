@@ -3,6 +3,7 @@
 #pragma once
 #include "kernels.h"
 #include "acs_k7.cuh"
+#include "acs_grp.cuh"
 
 namespace b200v {
 
@@ -43,6 +44,23 @@ template <> struct DecisionReader<DL_K7_INTERLEAVED> {
     __device__ __forceinline__ unsigned long long load(unsigned row) const { return __ldg(base + (size_t)row * stride); }
     __device__ __forceinline__ unsigned bit_of(unsigned long long word, unsigned row, unsigned state) const {
         return (unsigned)(word >> tab[row_phase[row] * k7::S + state]) & 1u;
+    }
+};
+
+// group family: one u64 per (row, frame, tx); the (tx, bit) of state n depends on the row's phase.
+template <> struct DecisionReader<DL_GRP_INTERLEAVED> {
+    const unsigned long long* base;   // + frame * TPF
+    size_t stride;                    // n_frames * TPF
+    const uint8_t* row_phase;
+    int nxb;
+    __device__ DecisionReader(const ChainbackArgs& a, int frame)
+        : base((const unsigned long long*)a.dec + (size_t)frame * (a.c.S >> 6)),
+          stride((size_t)a.n_frames * (a.c.S >> 6)), row_phase(a.row_phase), nxb(a.c.K - 1 - grp::NL) {}
+    __device__ __forceinline__ unsigned bit(unsigned row, unsigned state) const {
+        unsigned tx, b;
+        grp::decision_pos(nxb, row_phase[row], state, tx, b);
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(base + (size_t)row * stride + tx);
+        return (__ldg(p + (b >> 5)) >> (b & 31u)) & 1u;
     }
 };
 

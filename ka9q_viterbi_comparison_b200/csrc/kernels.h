@@ -34,13 +34,20 @@ cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_str
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
                           cudaStream_t st);
 
+// ---- group kernels for K=9 / K=15 (acs_grp.cu): decisions as one u64 per (row, frame, thread of the frame) ----
+bool grp_supported(const CodecParams& c);
+int grp_threads_per_frame(const CodecParams& c);
+cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
+                           cudaStream_t st);
+
 // ---- chainback (chainback.cu) ---------------------------------------------------------------------
 struct ChainbackArgs {
     CodecParams c;
     int layout;                 // DecisionLayout
     const void* dec;
     int dec_rows, row_words;    // DL_BALLOT_FRAME_MAJOR geometry
-    const uint8_t* row_phase;   // DL_K7_INTERLEAVED: phase of the step that wrote each row
+    const uint8_t* row_phase;   // DL_K7_INTERLEAVED / DL_GRP_INTERLEAVED: phase of the step that wrote each row
     int n_frames;
     const uint16_t* metrics;    // for the KA9Q615 return value
     uint8_t* out;               // device; frame f at out + f*out_stride

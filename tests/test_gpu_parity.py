@@ -287,3 +287,50 @@ def test_full_size_round_trip_properties():
                 qo, _ = q.decode(syms[f], nbits)
                 assert np.array_equal(outs[0].cpu().numpy().reshape(n_frames, -1)[f], qo)
                 q.close()
+
+
+@pytest.mark.parametrize("name", ["ka9q615", "spiral615", "wy_sse_u8_k15r6", "spiral29", "spiral49", "wy_sse_u8_k9r2",
+                                  "wy_sse_u8_k9r4", "ka9q29"])
+def test_long_frames_all_families(name):
+    """BASELINE-length frames (2048 bits): many renormalisations, lane rebasing of the group kernels, the
+    partial last group (T mod 5 != 0) and streaming across kernel launches at odd phases."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes = 256
+    T = nbytes * 8 + K - 1
+    n_frames = 3 if K == 15 else 35
+    sigma = 1.0 if K == 15 else 0.7
+    data, syms = make_batch(c, n_frames, nbytes, sigma, seed=0xA11)
+    refs = []
+    for f in range(n_frames):
+        q = o.Oracle(c, T)
+        q.init(0)
+        q.update(syms[f], T)
+        refs.append((q.decisions(0, T), q.metrics(), q.chainback(nbytes * 8, 0, return_code=True)))
+        q.close()
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        for v in variants(dec):
+            for chunks in ((T,), (1003, 2, T)):
+                dec.reset()
+                dec.set_variant(v)
+                dec.reset()
+                pos = 0
+                for ch in chunks:
+                    n = min(ch, T - pos)
+                    n -= (n % 2) if name.startswith("spiral") and len(chunks) > 1 else 0
+                    if n <= 0:
+                        continue
+                    if name.startswith("spiral") and len(chunks) > 1:
+                        break      # spiral restarts every update at row 0: streaming is not meaningful
+                    dec.update(syms[:, pos * R:(pos + n) * R])
+                    pos += n
+                if pos != T:
+                    continue
+                out = dec.chainback(nbytes * 8)
+                rcs = dec.chainback_results()
+                for f in range(n_frames):
+                    qd, qm, (qo, qrc) = refs[f]
+                    assert np.array_equal(dec.decisions(f, 0, T), qd), f"v{v} {chunks} frame {f}: decisions"
+                    assert np.array_equal(dec.metrics(f), qm), f"v{v} {chunks} frame {f}: metrics"
+                    assert np.array_equal(out[f], qo), f"v{v} {chunks} frame {f}: decoded bytes"
+                    assert int(rcs[f]) == qrc
