@@ -68,6 +68,7 @@ struct GrpArgs {
     uint16_t* metrics;             // canonical [n_frames][S]
     int n_frames;
     int C, thr, soft_hi, soft_lo;
+    int one;                       // 1 (a multiplier ptxas cannot fold: keeps the lo-path adds on the FMA pipe)
 };
 
 // scalar branch metric / complement of code word cw for one step's symbols (same formulas as policy.cuh)
@@ -187,27 +188,32 @@ __device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint
 }
 
 // ---- butterflies of one step in phase P -------------------------------------------------------------------
+// Pipe balance (ncu: the ALU pipe binds): only the hi-path candidates need the saturating VIADDMNMX -- the
+// survivor is min(lo path, hi path) <= hi path <= clamp, and when both saturate the reference's tie -> hi
+// decision is reproduced because the hi path equals the clamp -- so the lo-path adds are plain adds issued on
+// the FMA pipe (IMAD), and the decisions are accumulated with predicated FADDs (dpx.cuh: min_facc).
+struct DecAcc { float al, ah, bl, bh; };
+
 template <int POLICY, class CODE, int P, int KK>
 struct PairLoop {
-    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], uint32_t A, uint32_t clamp, uint32_t& acc0,
-                                               uint32_t& acc1) {
+    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], uint32_t A, uint32_t clamp, uint32_t one, DecAcc& d) {
         constexpr int NXB = CODE::K - 1 - NL;
         constexpr int XB = NL - 1 - P;
         constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
         constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
         uint32_t W, Wc;
         lds64(A ^ (c << 3), W, Wc);
-        const uint32_t m0 = __viaddmin_u16x2(w[iA], W, clamp), m1 = __viaddmin_u16x2(w[iB], Wc, clamp);
-        const uint32_t m2 = __viaddmin_u16x2(w[iA], Wc, clamp), m3 = __viaddmin_u16x2(w[iB], W, clamp);
+        const uint32_t m0 = add_fma(w[iA], one, W), m1 = __viaddmin_u16x2(w[iB], Wc, clamp);
+        const uint32_t m2 = add_fma(w[iA], one, Wc), m3 = __viaddmin_u16x2(w[iB], W, clamp);
         // decision = (min == hi path): tie -> 1 (viterbi615_sse2.cpp:145-148, spiral615.cpp:247-250, sse_u8.h:111-114)
-        w[iA] = min_acc<KK, 16 + KK, false>(m1, m0, acc0);
-        w[iB] = min_acc<KK, 16 + KK, false>(m3, m2, acc1);
-        PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, acc0, acc1);
+        w[iA] = min_facc<KK>(m1, m0, d.al, d.ah);
+        w[iB] = min_facc<KK>(m3, m2, d.bl, d.bh);
+        PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, one, d);
     }
 };
 template <int POLICY, class CODE, int P>
 struct PairLoop<POLICY, CODE, P, 16> {
-    __device__ __forceinline__ static void run(uint32_t (&)[NREG], uint32_t, uint32_t, uint32_t&, uint32_t&) {}
+    __device__ __forceinline__ static void run(uint32_t (&)[NREG], uint32_t, uint32_t, uint32_t, DecAcc&) {}
 };
 
 // exchange after a whole group: phase-5 layout (register q, lane, tx) = state (2tx+lane)*32 + q  ->  shared
@@ -278,9 +284,9 @@ template <int POLICY, class CODE, class CF, int P, bool EXCH>
 __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const GrpArgs& a, uint32_t sub_addr,
                                      uint32_t cx8, unsigned long long* dec_out, bool live, uint32_t met_addr,
                                      uint32_t* s_red, int& rpar, int tid, int tx) {
-    uint32_t acc0 = 0, acc1 = 0;
-    PairLoop<POLICY, CODE, P, 0>::run(w, sub_addr + cx8, fs.clamp, acc0, acc1);
-    if (live) *dec_out = (unsigned long long)acc0 | ((unsigned long long)acc1 << 32);
+    DecAcc d = { FDEC_ZERO, FDEC_ZERO, FDEC_ZERO, FDEC_ZERO };
+    PairLoop<POLICY, CODE, P, 0>::run(w, sub_addr + cx8, fs.clamp, (uint32_t)a.one, d);
+    if (live) *dec_out = (unsigned long long)fdec_pack(d.al, d.ah) | ((unsigned long long)fdec_pack(d.bl, d.bh) << 32);
     const uint32_t lm = local_min(w);
     const uint32_t w0 = w[0];
     if (EXCH) {
@@ -446,7 +452,7 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
     grp::GrpArgs a;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
-    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
+    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1;
     switch (grp::find_instance(c)) {
     case grp::I_KA9Q615: return grp::launch_one<P_KA9Q_S16_615, grp::CodeK15R6>(a, st);
     case grp::I_SPIRAL615: return grp::launch_one<P_SPIRAL_615, grp::CodeK15R6>(a, st);

@@ -13,14 +13,14 @@ template <int BIT_LO, int BIT_HI, bool NEG>
 __device__ __forceinline__ uint32_t min_acc(uint32_t a, uint32_t b, uint32_t& acc) {
     uint32_t s;
     if (NEG) {
-        asm("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+        asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
             "min.u16x2 %0, %2, %3;\n\t"
             "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %2;\n\t"
             "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
             "@!pv or.b32 %1, %1, %4;\n\t@!pu or.b32 %1, %1, %5;\n\t}"
             : "=&r"(s), "+r"(acc) : "r"(a), "r"(b), "n"(1u << BIT_LO), "n"(1u << BIT_HI));
     } else {
-        asm("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+        asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
             "min.u16x2 %0, %2, %3;\n\t"
             "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %2;\n\t"
             "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
@@ -28,6 +28,31 @@ __device__ __forceinline__ uint32_t min_acc(uint32_t a, uint32_t b, uint32_t& ac
             : "=&r"(s), "+r"(acc) : "r"(a), "r"(b), "n"(1u << BIT_LO), "n"(1u << BIT_HI));
     }
     return s;
+}
+
+// Same compare-select, but the two decisions are accumulated on the FMA pipe: a set decision adds 2^BIT to an
+// fp32 accumulator that starts at 2^23 (exact: at most 16 distinct powers of two below 2^16), leaving the ALU
+// pipe to the packed min/add instructions. fdec_pack() extracts the two 16-bit fields.
+template <int BIT>
+__device__ __forceinline__ uint32_t min_facc(uint32_t a, uint32_t b, float& acc_lo, float& acc_hi) {
+    uint32_t s;
+    asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+        "min.u16x2 %0, %3, %4;\n\t"
+        "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %3;\n\t"
+        "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
+        "@pv add.rn.f32 %1, %1, %5;\n\t@pu add.rn.f32 %2, %2, %5;\n\t}"
+        : "=&r"(s), "+f"(acc_lo), "+f"(acc_hi) : "r"(a), "r"(b), "f"((float)(1u << BIT)));
+    return s;
+}
+constexpr float FDEC_ZERO = 8388608.0f;   // 2^23
+__device__ __forceinline__ uint32_t fdec_pack(float acc_lo, float acc_hi) {
+    return __byte_perm(__float_as_uint(acc_lo), __float_as_uint(acc_hi), 0x5410);
+}
+// a + b on the FMA pipe (IMAD with a multiplier ptxas cannot fold); packed lanes must not overflow
+__device__ __forceinline__ uint32_t add_fma(uint32_t a, uint32_t one, uint32_t b) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+    return d;
 }
 
 }  // namespace b200v
