@@ -6,6 +6,10 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libb200viterbi.so")
+# the reference's per-codec C++ API on top of the C-ABI (include/ref_compat/): a separate library so that its
+# C++-linkage symbols never meet the reference's own objects in one link
+COMPAT_SRC = os.path.join(CSRC, "ref_compat.cpp")
+COMPAT_LIB_PATH = os.path.join(PKG_DIR, "libb200viterbi_compat.so")
 INCLUDE_DIR = os.path.join(os.path.dirname(PKG_DIR), "include")
 
 NVCC_FLAGS = [
@@ -17,7 +21,8 @@ NVCC_FLAGS = [
 
 
 def sources():
-    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cpp")))
+    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)
+                  if f.endswith((".cu", ".cpp")) and os.path.join(CSRC, f) != COMPAT_SRC)
 
 
 def _deps():
@@ -29,7 +34,7 @@ def _deps():
 
 
 def needs_build():
-    if not os.path.exists(LIB_PATH):
+    if not os.path.exists(LIB_PATH) or not os.path.exists(COMPAT_LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
     return any(os.path.getmtime(p) > t for p in _deps())
@@ -58,6 +63,12 @@ def build_library(force=False, verbose=False):
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
+    cxx = shutil.which("g++") or "g++"
+    res = subprocess.run([cxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-I", INCLUDE_DIR, "-o", COMPAT_LIB_PATH,
+                          COMPAT_SRC, "-L", PKG_DIR, "-lb200viterbi", "-Wl,-rpath,$ORIGIN"],
+                         capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("building libb200viterbi_compat.so failed:\n" + res.stdout + res.stderr)
     return LIB_PATH
 
 

@@ -136,6 +136,7 @@ struct b200v_batch {
     int variant = 1;             // kernel family in use (1 generic, 2 register-resident)
     int layout = DL_BALLOT_FRAME_MAJOR;
     bool has_fast = false;
+    bool generic_ok = true;      // the generic shared-memory family exists for this K
     int fast_layout = DL_BALLOT_FRAME_MAJOR;   // decision layout of the specialised family, if any
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev_u0 = nullptr, ev_u1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
@@ -144,6 +145,8 @@ struct b200v_batch {
     // device buffers
     void* d_dec = nullptr;       size_t dec_bytes = 0;
     uint16_t* d_metrics = nullptr;
+    // K=24 family: second ping-pong metric buffer, which buffer is current, per-step minima, pending adjustments
+    uint16_t* d_metrics2 = nullptr; int cur_metrics = 0; int* d_gmin = nullptr; int* d_adj = nullptr;
     uint8_t* d_cw = nullptr;
     uint8_t* d_row_phase = nullptr;   // K=7 register family: phase of the step that wrote each decision row
     int* d_results = nullptr;
@@ -156,7 +159,7 @@ static void free_all(b200v_batch* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
-    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase);
+    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase);
     cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
@@ -178,8 +181,8 @@ extern "C" b200v_batch* b200v_batch_create(int codec, int K, int R, const int* p
         fail(B200V_ERR_ARG, "frame_steps=%d n_frames=%d must be positive", frame_steps, n_frames);
         return nullptr;
     }
-    if (c.K > 16) {
-        fail(B200V_ERR_ARG, "K=%d: only K<=16 is implemented in this build (K=24 kernel family pending)", c.K);
+    if (c.K > 16 && c.policy != P_KA9Q_S16_224) {
+        fail(B200V_ERR_ARG, "K=%d: constraint lengths above 16 exist only for the ka9q viterbi224 policy", c.K);
         return nullptr;
     }
     b200v_batch* h = new (std::nothrow) b200v_batch();
@@ -210,7 +213,7 @@ static int create_impl(b200v_batch* h, int starting_state) {
 
     // code word of butterfly j: bit i = parity((2j) & poly_i) (viterbi27_sse2.cpp:61-70,
     // viterbi_branch_table.h:44-54); spiral: a negative polynomial inverts the bit (spiral27.cpp:69)
-    const int H = c.S / 2;
+    const int H = c.K > 16 ? 0 : c.S / 2;
     std::vector<uint8_t> cw((size_t)H, 0);
     for (int i = 0; i < c.R; i++) {
         const int p = c.poly[i];
@@ -219,10 +222,19 @@ static int create_impl(b200v_batch* h, int starting_state) {
         for (int j = 0; j < H; j++)
             cw[j] |= (uint8_t)((((unsigned)popcount32((2u * (uint32_t)j) & ap) & 1u) ^ (inv ? 1u : 0u)) << i);
     }
-    CUDA_TRY(cudaMalloc(&h->d_cw, (size_t)H));
-    CUDA_TRY(cudaMemcpyAsync(h->d_cw, cw.data(), (size_t)H, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaMalloc(&h->d_cw, (size_t)(H ? H : 1)));
+    if (H) CUDA_TRY(cudaMemcpyAsync(h->d_cw, cw.data(), (size_t)H, cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));   // cw is a local vector
 
+    if (c.K > 16) {     // K=24 family: no shared-memory kernel, no code-word table (computed from the polynomials)
+        CUDA_TRY(cudaMalloc(&h->d_metrics2, (size_t)h->n_frames * c.S * sizeof(uint16_t)));
+        CUDA_TRY(cudaMalloc(&h->d_gmin, (size_t)h->n_frames * h->dec_rows * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&h->d_adj, (size_t)h->n_frames * sizeof(int)));
+        CUDA_TRY(cudaMalloc(&h->d_row_phase, (size_t)h->dec_rows));
+        h->fast_layout = DL_CANONICAL; h->has_fast = true; h->generic_ok = false;
+        h->variant = 2; h->layout = DL_CANONICAL;
+        return b200v_batch_init(h, starting_state);
+    }
     const GenericPlan plan = generic_plan(c);
     if (plan.smem_bytes > 227 * 1024)
         return fail(B200V_ERR_ARG, "K=%d needs %d bytes of shared memory per block", c.K, plan.smem_bytes);
@@ -248,7 +260,7 @@ extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
     if (variant == 0) variant = h->has_fast ? 2 : 1;
     if (variant != h->variant && h->cursor != 0)
         return fail(B200V_ERR_STATE, "the kernel family can only change right after init (decision layouts differ)");
-    if (variant == 1) { h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
+    if (variant == 1 && h->generic_ok) { h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
     if (variant == 2 && h->has_fast) { h->variant = 2; h->layout = h->fast_layout; return B200V_OK; }
     return fail(B200V_ERR_ARG, "kernel family %d is not available for this instance", variant);
 }
@@ -260,6 +272,7 @@ extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     CUDA_TRY(launch_init_metrics(h->d_metrics, h->n_frames, h->c, starting_state, h->stream));
     h->launches++;
     h->cursor = 0;
+    h->cur_metrics = 0;
     return B200V_OK;
 }
 
@@ -278,7 +291,11 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
     CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
-    if (nsteps > 0 && h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
+    if (nsteps > 0 && h->layout == DL_CANONICAL) {
+        CUDA_TRY(launch_acs_k24(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (uint32_t*)h->d_dec, h->dec_rows,
+                                h->d_metrics, h->d_metrics2, &h->cur_metrics, h->d_gmin, h->d_adj, h->n_frames,
+                                &h->launches, h->stream));
+    } else if (nsteps > 0 && h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
         CUDA_TRY(launch_acs_grp(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (unsigned long long*)h->d_dec,
                                 h->d_row_phase, h->d_metrics, h->n_frames, h->stream));
         h->launches++;
@@ -339,7 +356,7 @@ extern "C" int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t
     ChainbackArgs a{};
     a.c = c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
     a.row_phase = h->d_row_phase;
-    a.n_frames = h->n_frames; a.metrics = h->d_metrics; a.out = d_data; a.out_stride = frame_stride_bytes;
+    a.n_frames = h->n_frames; a.metrics = h->cur_metrics ? h->d_metrics2 : h->d_metrics; a.out = d_data; a.out_stride = frame_stride_bytes;
     a.nbits = nbits; a.endstate = endstate; a.results = h->d_results;
     CUDA_TRY(cudaEventRecord(h->ev_c0, h->stream));
     CUDA_TRY(launch_chainback(a, h->stream));
@@ -404,6 +421,14 @@ extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, i
     const int S = h->c.S;
     const size_t nb = (size_t)S / 8;
     memset(out, 0, nb * nsteps);
+    if (h->layout == DL_CANONICAL) {
+        const uint32_t* src = (const uint32_t*)h->d_dec + ((size_t)frame * h->dec_rows + step0) * h->row_words;
+        if (nsteps > 0) {
+            CUDA_TRY(cudaMemcpyAsync(out, src, nb * nsteps, cudaMemcpyDeviceToHost, h->stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        }
+        return B200V_OK;
+    }
     if (h->layout == DL_BALLOT_FRAME_MAJOR) {
         std::vector<uint32_t> rows((size_t)nsteps * h->row_words);
         const uint32_t* src = (const uint32_t*)h->d_dec + ((size_t)frame * h->dec_rows + step0) * h->row_words;
@@ -469,7 +494,8 @@ extern "C" int b200v_batch_get_metrics(b200v_batch* h, int frame, void* out) {
     CUDA_TRY(cudaSetDevice(h->device));
     const int S = h->c.S;
     std::vector<uint16_t> m((size_t)S);
-    CUDA_TRY(cudaMemcpyAsync(m.data(), h->d_metrics + (size_t)frame * S, (size_t)S * 2, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(m.data(), (h->cur_metrics ? h->d_metrics2 : h->d_metrics) + (size_t)frame * S, (size_t)S * 2,
+                             cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     if (h->c.metric_bytes == 2) memcpy(out, m.data(), (size_t)S * 2);
     else for (int i = 0; i < S; i++) ((uint8_t*)out)[i] = (uint8_t)m[i];

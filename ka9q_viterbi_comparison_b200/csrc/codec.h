@@ -43,6 +43,8 @@ enum DecisionLayout : int {
     // group family (K=9, K=15; acs_grp.cuh): one u64 per (step, frame, thread-of-frame), frame-interleaved:
     // dec[(step*n_frames + frame)*TPF + tx]; bit positions depend on the phase (step mod 5) of the row
     DL_GRP_INTERLEAVED = 2,
+    // K=24 family (acs_k24.cu): the canonical vector itself, frame-major: bit n of dec[frame][step][S/32 words]
+    DL_CANONICAL = 3,
 };
 
 static inline bool policy_is_spiral(int p) { return p == P_SPIRAL_R2 || p == P_SPIRAL_R4 || p == P_SPIRAL_615; }

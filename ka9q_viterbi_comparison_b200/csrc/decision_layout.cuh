@@ -47,6 +47,16 @@ template <> struct DecisionReader<DL_K7_INTERLEAVED> {
     }
 };
 
+template <> struct DecisionReader<DL_CANONICAL> {
+    const uint32_t* base;
+    int row_words;
+    __device__ DecisionReader(const ChainbackArgs& a, int frame)
+        : base((const uint32_t*)a.dec + (size_t)frame * a.dec_rows * a.row_words), row_words(a.row_words) {}
+    __device__ __forceinline__ unsigned bit(unsigned row, unsigned state) const {
+        return (__ldg(base + (size_t)row * row_words + (state >> 5)) >> (state & 31u)) & 1u;
+    }
+};
+
 // group family: one u64 per (row, frame, tx); the (tx, bit) of state n depends on the row's phase.
 template <> struct DecisionReader<DL_GRP_INTERLEAVED> {
     const unsigned long long* base;   // + frame * TPF

@@ -41,6 +41,11 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
                            cudaStream_t st);
 
+// ---- K=24 (acs_k24.cu): one launch per trellis step, ping-pong metric buffers, canonical decision rows ----
+cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                           uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
+                           int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st);
+
 // ---- chainback (chainback.cu) ---------------------------------------------------------------------
 struct ChainbackArgs {
     CodecParams c;
