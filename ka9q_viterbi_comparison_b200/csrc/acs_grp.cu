@@ -49,7 +49,9 @@ struct Cfg {
     static constexpr int FPB = TPF >= 32 ? 1 : 128 / TPF;       // frames per block
     static constexpr int THREADS = TPF * FPB;
     static constexpr int MET_STRIDE = S * 2 + (TPF < 32 ? 16 : 0);   // bytes of exchange buffer per frame
-    static constexpr int SUBTAB = NCW * 8;                      // one step's table: NCW x {W, Wc}
+    static constexpr bool modular = (POLICY == P_KA9Q_U8_MOD);
+    static constexpr int ESHIFT = modular ? 4 : 3;              // table entry: {W, Wc} or {W, Wc, X0, X1}
+    static constexpr int SUBTAB = NCW << ESHIFT;                // one step's table
     static constexpr int TAB_BYTES = 2 * NL * SUBTAB;           // two groups (double buffer) x five steps
     static constexpr int RED_WORDS = 2 * 16;                    // block reduction scratch (TPF >= 32)
     static constexpr int SMEM = FPB * TAB_BYTES + FPB * MET_STRIDE + RED_WORDS * 4;
@@ -88,10 +90,11 @@ __device__ __forceinline__ void bm_eval(unsigned cw, const int* sym, const GrpAr
 #pragma unroll
         for (int i = 0; i < R; i++) s += ((cw >> i) & 1u) ? (sym[i] ^ 255) : sym[i];
         v = s;
-    } else if (POLICY == P_SPIRAL_R2) {
+    } else if (POLICY == P_SPIRAL_R2 || POLICY == P_KA9Q_U8_MOD) {
         const int x0 = (cw & 1u) ? (sym[0] ^ 255) : sym[0];
         const int x1 = (cw & 2u) ? (sym[1] ^ 255) : sym[1];
-        v = (((x0 + x1 + 1) >> 1) >> 2) & 63;
+        const int avg = (x0 + x1 + 1) >> 1;
+        v = POLICY == P_KA9Q_U8_MOD ? (avg >> 4) : ((avg >> 2) & 63);
     } else {   // P_SPIRAL_R4, P_SPIRAL_615
         int s = 0;
 #pragma unroll
@@ -111,6 +114,9 @@ __device__ __forceinline__ void lds64(uint32_t addr, uint32_t& x, uint32_t& y) {
 }
 __device__ __forceinline__ void sts64(uint32_t addr, uint32_t x, uint32_t y) {
     asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void lds128(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
 }
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v;
@@ -201,6 +207,22 @@ struct PairLoop {
         constexpr int XB = NL - 1 - P;
         constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
         constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
+        if constexpr (POLICY == P_KA9Q_U8_MOD) {
+            // ka9q modular policy (viterbi29_sse2.cpp:137-158): lanes hold metric << 8, so 16-bit wrap-around is
+            // the reference's mod-256 arithmetic and the s16 sign of a difference is its (int8) sign.
+            //   t0 = m0 - m1 = (A + ~B) + X0,  X0 = W - Wc + 1;   t1 = m2 - m3 = (A + ~B) + X1,  X1 = Wc - W + 1
+            //   decision = t > 0 (tie -> 0);  survivor = hi path + min(t, 0)
+            uint32_t W, Wc, X0, X1;
+            lds128(A ^ (c << 4), W, Wc, X0, X1);
+            const uint32_t dd = __vadd2(w[iA], ~w[iB]);
+            const uint32_t m1 = __vadd2(w[iB], Wc), m3 = __vadd2(w[iB], W);
+            const uint32_t z0 = relu_neg_facc<KK>(__vadd2(dd, X0), d.al, d.ah);
+            const uint32_t z1 = relu_neg_facc<KK>(__vadd2(dd, X1), d.bl, d.bh);
+            w[iA] = __vadd2(m1, z0);
+            w[iB] = __vadd2(m3, z1);
+            PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, one, d);
+            return;
+        }
         uint32_t W, Wc;
         lds64(A ^ (c << 3), W, Wc);
         const uint32_t m0 = add_fma(w[iA], one, W), m1 = __viaddmin_u16x2(w[iB], Wc, clamp);
@@ -267,7 +289,15 @@ __device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned cha
         bm_eval<POLICY, R>(c1, sym, a, b1, m1);
         bm_eval<POLICY, R>(c2, sym, a, b2, m2);
         const uint32_t st = buf + (uint32_t)s * CF::SUBTAB;
-        if (D) {
+        if (CF::modular) {       // scaled by 256; X0 = W - Wc + 1, X1 = Wc - W + 1 per 16-bit lane
+            const uint32_t d2 = D ? b2 : b1, e2 = D ? m2 : m1;     // second lane of entry c1 (entry c2 mirrors it)
+            const uint32_t Wa = pack2(b1 << 8, d2 << 8), Wca = pack2(m1 << 8, e2 << 8);
+            const uint32_t Wb = pack2(b2 << 8, (D ? b1 : b2) << 8), Wcb = pack2(m2 << 8, (D ? m1 : m2) << 8);
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(st + c1 * 16), "r"(Wa), "r"(Wca),
+                         "r"(__vadd2(__vsub2(Wa, Wca), 0x00010001u)), "r"(__vadd2(__vsub2(Wca, Wa), 0x00010001u)) : "memory");
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(st + c2 * 16), "r"(Wb), "r"(Wcb),
+                         "r"(__vadd2(__vsub2(Wb, Wcb), 0x00010001u)), "r"(__vadd2(__vsub2(Wcb, Wb), 0x00010001u)) : "memory");
+        } else if (D) {
             sts64(st + c1 * 8, pack2(b1, b2), pack2(m1, m2));
             sts64(st + c2 * 8, pack2(b2, b1), pack2(m2, m1));
         } else {
@@ -287,6 +317,14 @@ __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const 
     DecAcc d = { FDEC_ZERO, FDEC_ZERO, FDEC_ZERO, FDEC_ZERO };
     PairLoop<POLICY, CODE, P, 0>::run(w, sub_addr + cx8, fs.clamp, (uint32_t)a.one, d);
     if (live) *dec_out = (unsigned long long)fdec_pack(d.al, d.ah) | ((unsigned long long)fdec_pack(d.bl, d.bh) << 32);
+    if constexpr (CF::modular) {
+        if (EXCH) {
+            exchange_store<CF>(w, met_addr, tx);
+            if (CF::TPF < 32) __syncwarp(); else __syncthreads();
+            exchange_load<CF>(w, met_addr, tx);
+        }
+        return;
+    }
     const uint32_t lm = local_min(w);
     const uint32_t w0 = w[0];
     if (EXCH) {
@@ -328,11 +366,13 @@ acs_grp_kernel(const GrpArgs a) {
         for (int q = 0; q < NREG; q++) {
             w[q] = g32[q * CF::TPF + tx];
             if (CF::s16) w[q] ^= 0x80008000u;          // s16 -> biased u16
+            if (CF::modular) w[q] = (w[q] << 8) & 0xff00ff00u;
         }
     }
     FrameState fs;
     fs.base = 0;
-    {   // bring the lanes down to the bottom of the 16-bit window
+    fs.clamp = 0;
+    if (!CF::modular) {   // bring the lanes down to the bottom of the 16-bit window
         uint32_t gmin, g0;
         frame_min<CF>(local_min(w), w[0], s_red, rpar, tid, gmin, g0);
         const uint32_t sub = gmin * 0x10001u;
@@ -349,7 +389,7 @@ acs_grp_kernel(const GrpArgs a) {
         unsigned c = 0;
 #pragma unroll
         for (int i = 0; i < CF::R; i++) c |= (unsigned)(__popc(((unsigned)tx << (p + 2)) & CODE::poly(i)) & 1) << i;
-        cx8[p] = c << 3;
+        cx8[p] = c << CF::ESHIFT;
     }
 
     const unsigned char* sp = a.syms + (size_t)frame * a.sym_stride;
@@ -386,8 +426,9 @@ acs_grp_kernel(const GrpArgs a) {
             int q;
             unsigned xx;
             locate_state(CF::NXB, pf, n, q, xx);
-            const int tb = (int)raw[(q * CF::TPF + (int)(xx >> 1)) * 2 + (int)(xx & 1u)] + fs.base;
-            gm[n] = (uint16_t)(CF::s16 ? (tb ^ 0x8000) : tb);
+            const int rv = (int)raw[(q * CF::TPF + (int)(xx >> 1)) * 2 + (int)(xx & 1u)];
+            const int tb = rv + fs.base;
+            gm[n] = (uint16_t)(CF::modular ? (rv >> 8) : CF::s16 ? (tb ^ 0x8000) : tb);
         }
     }
 }
@@ -415,7 +456,7 @@ static bool same_code(const CodecParams& c) {
     return true;
 }
 
-enum Instance { I_NONE = -1, I_KA9Q615, I_SPIRAL615, I_WY8_K15R6, I_SPIRAL29, I_WY8_K9R2, I_SPIRAL49, I_WY8_K9R4 };
+enum Instance { I_NONE = -1, I_KA9Q29, I_KA9Q615, I_SPIRAL615, I_WY8_K15R6, I_SPIRAL29, I_WY8_K9R2, I_SPIRAL49, I_WY8_K9R4 };
 
 static int find_instance(const CodecParams& c) {
     if (same_code<CodeK15R6>(c)) {
@@ -423,6 +464,7 @@ static int find_instance(const CodecParams& c) {
         if (c.policy == P_SPIRAL_615) return I_SPIRAL615;
         if (c.policy == P_WY_U8) return I_WY8_K15R6;
     } else if (same_code<CodeK9R2>(c)) {
+        if (c.policy == P_KA9Q_U8_MOD) return I_KA9Q29;
         if (c.policy == P_SPIRAL_R2) return I_SPIRAL29;
         if (c.policy == P_WY_U8) return I_WY8_K9R2;
     } else if (same_code<CodeK9R4>(c)) {
@@ -454,6 +496,7 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1;
     switch (grp::find_instance(c)) {
+    case grp::I_KA9Q29: return grp::launch_one<P_KA9Q_U8_MOD, grp::CodeK9R2>(a, st);
     case grp::I_KA9Q615: return grp::launch_one<P_KA9Q_S16_615, grp::CodeK15R6>(a, st);
     case grp::I_SPIRAL615: return grp::launch_one<P_SPIRAL_615, grp::CodeK15R6>(a, st);
     case grp::I_WY8_K15R6: return grp::launch_one<P_WY_U8, grp::CodeK15R6>(a, st);

@@ -333,7 +333,9 @@ static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-using CodeK7R2 = Code<2, 0x6d, 0x4f, 0, 0>;   // src/main.cpp:367 (Voyager)
+using CodeK7R2 = Code<2, 0x6d, 0x4f, 0, 0>;       // src/main.cpp:367 (Voyager)
+using CodeK7R4 = Code<4, 121, 117, 91, 111>;      // src/main.cpp:377
+using CodeK7R3 = Code<3, 91, 117, 121, 0>;        // williamyang_viterbi_lib/examples/helpers/common_codes.h (LTE)
 
 // index of the instantiation matching (policy, R, poly), or -1
 static int find_instance(const CodecParams& c) {
@@ -343,6 +345,11 @@ static int find_instance(const CodecParams& c) {
         if (c.policy == P_SPIRAL_R2) return 1;
         if (c.policy == P_WY_U8) return 2;
     }
+    if (c.R == 4 && c.poly[0] == 121 && c.poly[1] == 117 && c.poly[2] == 91 && c.poly[3] == 111) {
+        if (c.policy == P_SPIRAL_R4) return 3;
+        if (c.policy == P_WY_U8) return 4;
+    }
+    if (c.R == 3 && c.poly[0] == 91 && c.poly[1] == 117 && c.poly[2] == 121 && c.policy == P_WY_U8) return 5;
     return -1;
 }
 
@@ -367,6 +374,9 @@ cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_str
     case 0: return k7::launch_one<P_KA9Q_U8_MOD, k7::CodeK7R2>(a, st);
     case 1: return k7::launch_one<P_SPIRAL_R2, k7::CodeK7R2>(a, st);
     case 2: return k7::launch_one<P_WY_U8, k7::CodeK7R2>(a, st);
+    case 3: return k7::launch_one<P_SPIRAL_R4, k7::CodeK7R4>(a, st);
+    case 4: return k7::launch_one<P_WY_U8, k7::CodeK7R4>(a, st);
+    case 5: return k7::launch_one<P_WY_U8, k7::CodeK7R3>(a, st);
     default: return cudaErrorInvalidValue;
     }
 }
