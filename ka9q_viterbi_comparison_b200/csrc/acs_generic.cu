@@ -45,9 +45,9 @@ __global__ void acs_generic_kernel(const GenericArgs a, const int tpf, const int
     const CodecParams& c = a.c;
     const int S = c.S, H = S >> 1, R = c.R, nbm = 1 << R;
     const int fl = threadIdx.x / tpf, lt = threadIdx.x - fl * tpf;
-    const int frame_raw = blockIdx.x * fpb + fl;
-    const bool live = frame_raw < a.n_frames;
-    const int frame = live ? frame_raw : a.n_frames - 1;
+    const int fidx = blockIdx.x * fpb + fl;
+    const bool live = fidx < a.count;
+    const int frame = a.frame0 + (live ? fidx : a.count - 1);
 
     // ---- shared memory carve-up ----
     // [cw: H bytes, padded to 16] then per frame slot: met[2][S] u16 | bm[2][nbm] int | decrow[2][row_words] u32 | scratch[32]
@@ -156,7 +156,7 @@ __global__ void init_metrics_kernel(uint16_t* metrics, int n_frames, int S, int 
 
 template <int POLICY>
 cudaError_t launch_policy(const GenericArgs& a, const GenericPlan& p, cudaStream_t st) {
-    const int blocks = (a.n_frames + p.frames_per_block - 1) / p.frames_per_block;
+    const int blocks = (a.count + p.frames_per_block - 1) / p.frames_per_block;
     const int threads = p.threads_per_frame * p.frames_per_block;
     cudaError_t e;
     if (p.threads_per_frame == 32) {
@@ -189,7 +189,7 @@ GenericPlan generic_plan(const CodecParams& c) {
 }
 
 cudaError_t launch_acs_generic(const GenericArgs& a, cudaStream_t st) {
-    if (a.n_frames <= 0) return cudaSuccess;
+    if (a.count <= 0) return cudaSuccess;
     const GenericPlan p = generic_plan(a.c);
     switch (a.c.policy) {
     case P_KA9Q_U8_MOD: return launch_policy<P_KA9Q_U8_MOD>(a, p, st);

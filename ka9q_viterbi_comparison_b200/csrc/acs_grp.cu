@@ -69,6 +69,7 @@ struct GrpArgs {
     uint8_t* row_phase;
     uint16_t* metrics;             // canonical [n_frames][S]
     int n_frames;
+    int frame0, count;             // frames [frame0, frame0 + count) of the n_frames-wide layout
     int C, thr, soft_hi, soft_lo;
     int one;                       // 1 (a multiplier ptxas cannot fold: keeps the lo-path adds on the FMA pipe)
 };
@@ -344,9 +345,9 @@ acs_grp_kernel(const GrpArgs a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x;
     const int fl = tid / CF::TPF, tx = tid % CF::TPF;
-    const int frame_raw = blockIdx.x * CF::FPB + fl;
-    const bool live = frame_raw < a.n_frames;
-    const int frame = live ? frame_raw : a.n_frames - 1;
+    const int fidx = blockIdx.x * CF::FPB + fl;
+    const bool live = fidx < a.count;
+    const int frame = a.frame0 + (live ? fidx : a.count - 1);
 
     const uint32_t tab_addr = smem_u32(smem) + (uint32_t)fl * CF::TAB_BYTES;
     unsigned char* met_ptr = smem + CF::FPB * CF::TAB_BYTES + (size_t)fl * CF::MET_STRIDE;
@@ -439,7 +440,7 @@ static cudaError_t launch_one(const GrpArgs& a, cudaStream_t st) {
     auto k = acs_grp_kernel<POLICY, CODE>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SMEM);
     if (e != cudaSuccess) return e;
-    const int blocks = (a.n_frames + CF::FPB - 1) / CF::FPB;
+    const int blocks = (a.count + CF::FPB - 1) / CF::FPB;
     k<<<blocks, CF::THREADS, CF::SMEM, st>>>(a);
     return cudaGetLastError();
 }
@@ -489,11 +490,12 @@ int grp_threads_per_frame(const CodecParams& c) { return 1 << (c.K - 1 - grp::NL
 
 cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                           cudaStream_t st) {
-    if (n_frames <= 0 || nsteps <= 0) return cudaSuccess;
+                           int frame0, int count, cudaStream_t st) {
+    if (count <= 0 || nsteps <= 0) return cudaSuccess;
     grp::GrpArgs a;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
+    a.frame0 = frame0; a.count = count;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1;
     switch (grp::find_instance(c)) {
     case grp::I_KA9Q29: return grp::launch_one<P_KA9Q_U8_MOD, grp::CodeK9R2>(a, st);

@@ -96,6 +96,7 @@ struct K7Args {
     uint8_t* row_phase;            // phase of the step that produced each row
     uint16_t* metrics;             // canonical [n_frames][64] (reference metric values)
     int n_frames;
+    int frame0, count;             // frames [frame0, frame0 + count) of the n_frames-wide layout
     int C, thr, soft_hi, soft_lo;
 };
 
@@ -226,11 +227,12 @@ __device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE
 template <int POLICY, class CODE>
 __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     constexpr int R = CODE::R;
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int f = a.frame0 + idx;
     if (blockIdx.x == 0) {   // phase of every decision row this launch writes (read by chainback)
         for (int t = threadIdx.x; t < a.nsteps; t += blockDim.x) a.row_phase[a.step0 + t] = (uint8_t)(t % NB);
     }
-    if (f >= a.n_frames) return;
+    if (idx >= a.count) return;
 
     // ---- load canonical metrics into the phase-0 layout: register i = states (2i, 2i+1) ----
     uint32_t w[NW];
@@ -328,7 +330,7 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
 template <int POLICY, class CODE>
 static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
     const int threads = 128;
-    const int blocks = (a.n_frames + threads - 1) / threads;
+    const int blocks = (a.count + threads - 1) / threads;
     acs_k7_kernel<POLICY, CODE><<<blocks, threads, 0, st>>>(a);
     return cudaGetLastError();
 }
@@ -364,11 +366,12 @@ bool k7_supported(const CodecParams& c) {
 
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          cudaStream_t st) {
-    if (n_frames <= 0 || nsteps <= 0) return cudaSuccess;
+                          int frame0, int count, cudaStream_t st) {
+    if (count <= 0 || nsteps <= 0) return cudaSuccess;
     k7::K7Args a;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
+    a.frame0 = frame0; a.count = count;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
     switch (k7::find_instance(c)) {
     case 0: return k7::launch_one<P_KA9Q_U8_MOD, k7::CodeK7R2>(a, st);

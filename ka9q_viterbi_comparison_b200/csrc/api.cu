@@ -139,6 +139,9 @@ struct b200v_batch {
     bool generic_ok = true;      // the generic shared-memory family exists for this K
     int fast_layout = DL_BALLOT_FRAME_MAJOR;   // decision layout of the specialised family, if any
     cudaStream_t own_stream = nullptr, stream = nullptr;
+    static constexpr int NPIPE = 4;
+    cudaStream_t pipe[NPIPE] = { nullptr, nullptr, nullptr, nullptr };   // b200v_batch_decode's chunk pipeline
+    cudaEvent_t ev_pipe = nullptr;
     cudaEvent_t ev_u0 = nullptr, ev_u1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
     bool timed_update = false, timed_chainback = false;
     long long launches = 0;
@@ -165,6 +168,8 @@ static void free_all(b200v_batch* h) {
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
     if (h->ev_c0) cudaEventDestroy(h->ev_c0);
     if (h->ev_c1) cudaEventDestroy(h->ev_c1);
+    for (int i = 0; i < b200v_batch::NPIPE; i++) if (h->pipe[i]) cudaStreamDestroy(h->pipe[i]);
+    if (h->ev_pipe) cudaEventDestroy(h->ev_pipe);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }
@@ -276,6 +281,35 @@ extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     return B200V_OK;
 }
 
+// Launch the ACS kernel of the instance's family for frames [f0, f0 + cnt) on stream st.
+static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride, int nsteps, int step0, int f0, int cnt,
+                               cudaStream_t st) {
+    const CodecParams& c = h->c;
+    if (nsteps <= 0 || cnt <= 0) return B200V_OK;
+    if (h->layout == DL_CANONICAL) {
+        if (f0 != 0 || cnt != h->n_frames) return fail(B200V_ERR_STATE, "the K=24 family works on whole batches");
+        CUDA_TRY(launch_acs_k24(c, d_syms, stride, nsteps, step0, (uint32_t*)h->d_dec, h->dec_rows,
+                                h->d_metrics, h->d_metrics2, &h->cur_metrics, h->d_gmin, h->d_adj, h->n_frames,
+                                &h->launches, st));
+    } else if (h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
+        CUDA_TRY(launch_acs_grp(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
+                                h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
+        h->launches++;
+    } else if (h->variant == 2) {
+        CUDA_TRY(launch_acs_k7(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
+                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
+        h->launches++;
+    } else {
+        GenericArgs a{};
+        a.c = c; a.syms = d_syms; a.sym_stride = stride; a.nsteps = nsteps; a.step0 = step0;
+        a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
+        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
+        CUDA_TRY(launch_acs_generic(a, st));
+        h->launches++;
+    }
+    return B200V_OK;
+}
+
 extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t frame_stride_bytes, int nsteps) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     if (nsteps < 0 || (!d_syms && nsteps > 0)) return fail(B200V_ERR_ARG, "bad symbol buffer / step count");
@@ -291,26 +325,8 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
     CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
-    if (nsteps > 0 && h->layout == DL_CANONICAL) {
-        CUDA_TRY(launch_acs_k24(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (uint32_t*)h->d_dec, h->dec_rows,
-                                h->d_metrics, h->d_metrics2, &h->cur_metrics, h->d_gmin, h->d_adj, h->n_frames,
-                                &h->launches, h->stream));
-    } else if (nsteps > 0 && h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
-        CUDA_TRY(launch_acs_grp(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (unsigned long long*)h->d_dec,
-                                h->d_row_phase, h->d_metrics, h->n_frames, h->stream));
-        h->launches++;
-    } else if (nsteps > 0 && h->variant == 2) {
-        CUDA_TRY(launch_acs_k7(c, d_syms, frame_stride_bytes, nsteps, h->cursor, (unsigned long long*)h->d_dec,
-                               h->d_row_phase, h->d_metrics, h->n_frames, h->stream));
-        h->launches++;
-    } else if (nsteps > 0) {
-        GenericArgs a{};
-        a.c = c; a.syms = d_syms; a.sym_stride = frame_stride_bytes; a.nsteps = nsteps; a.step0 = h->cursor;
-        a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
-        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames;
-        CUDA_TRY(launch_acs_generic(a, h->stream));
-        h->launches++;
-    }
+    int rc = launch_update_range(h, d_syms, frame_stride_bytes, nsteps, h->cursor, 0, h->n_frames, h->stream);
+    if (rc) return rc;
     CUDA_TRY(cudaEventRecord(h->ev_u1, h->stream));
     h->timed_update = true;
     h->cursor += nsteps;
@@ -343,6 +359,19 @@ extern "C" int b200v_batch_update(b200v_batch* h, const void* syms, size_t frame
     return B200V_OK;
 }
 
+static int launch_chainback_range(b200v_batch* h, uint8_t* d_data, size_t stride, unsigned nbits, unsigned endstate,
+                                  int f0, int cnt, cudaStream_t st) {
+    ChainbackArgs a{};
+    a.c = h->c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
+    a.row_phase = h->d_row_phase;
+    a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
+    a.metrics = h->cur_metrics ? h->d_metrics2 : h->d_metrics; a.out = d_data; a.out_stride = stride;
+    a.nbits = nbits; a.endstate = endstate; a.results = h->d_results;
+    CUDA_TRY(launch_chainback(a, st));
+    h->launches++;
+    return B200V_OK;
+}
+
 extern "C" int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t frame_stride_bytes,
                                          unsigned nbits, unsigned endstate) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
@@ -353,14 +382,9 @@ extern "C" int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t
         return fail(B200V_ERR_STATE, "chainback of %u bits needs %u decision rows, %d allocated", nbits,
                     rows_needed, h->dec_rows);
     CUDA_TRY(cudaSetDevice(h->device));
-    ChainbackArgs a{};
-    a.c = c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
-    a.row_phase = h->d_row_phase;
-    a.n_frames = h->n_frames; a.metrics = h->cur_metrics ? h->d_metrics2 : h->d_metrics; a.out = d_data; a.out_stride = frame_stride_bytes;
-    a.nbits = nbits; a.endstate = endstate; a.results = h->d_results;
     CUDA_TRY(cudaEventRecord(h->ev_c0, h->stream));
-    CUDA_TRY(launch_chainback(a, h->stream));
-    h->launches++;
+    int rc = launch_chainback_range(h, d_data, frame_stride_bytes, nbits, endstate, 0, h->n_frames, h->stream);
+    if (rc) return rc;
     CUDA_TRY(cudaEventRecord(h->ev_c1, h->stream));
     h->timed_chainback = true;
     return B200V_OK;
@@ -393,14 +417,60 @@ extern "C" int b200v_batch_chainback_results(b200v_batch* h, int* results) {
     return B200V_OK;
 }
 
+// Batch entry point. Large batches are cut into chunks of frames that flow through NPIPE streams, each chunk
+// doing H2D copy -> update -> chainback -> D2H copy on its stream, so that the copies of one chunk overlap the
+// kernels of another (the path is PCIe-bound end to end: R*T symbol bytes in per decoded bit).
 extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
-    int rc = b200v_batch_init(h, 0);
+    if (!syms || (!data && nbits)) return fail(B200V_ERR_ARG, "NULL buffer");
+    const CodecParams& c = h->c;
+    const size_t srow = (size_t)h->frame_steps * c.R * c.sym_bytes;
+    const size_t orow = (nbits + 7) / 8;
+    const int min_chunk = 2048;
+    if (h->layout == DL_CANONICAL || h->n_frames < 2 * min_chunk || orow == 0) {
+        int rc = b200v_batch_init(h, 0);
+        if (rc) return rc;
+        rc = b200v_batch_update(h, syms, srow, h->frame_steps);
+        if (rc) return rc;
+        return b200v_batch_chainback(h, data, orow, nbits, 0);
+    }
+    const unsigned rows_needed = nbits + (unsigned)(c.K - 1);
+    if (rows_needed > (unsigned)h->dec_rows)
+        return fail(B200V_ERR_STATE, "chainback of %u bits needs %u decision rows, %d allocated", nbits,
+                    rows_needed, h->dec_rows);
+    CUDA_TRY(cudaSetDevice(h->device));
+    int rc = ensure_stage(&h->d_syms_stage, &h->syms_stage_bytes, srow * h->n_frames);
     if (rc) return rc;
-    const size_t srow = (size_t)h->frame_steps * h->c.R * h->c.sym_bytes;
-    rc = b200v_batch_update(h, syms, srow, h->frame_steps);
+    rc = ensure_stage((void**)&h->d_out_stage, &h->out_stage_bytes, orow * h->n_frames);
     if (rc) return rc;
-    return b200v_batch_chainback(h, data, (nbits + 7) / 8, nbits, 0);
+    for (int i = 0; i < b200v_batch::NPIPE; i++)
+        if (!h->pipe[i]) CUDA_TRY(cudaStreamCreateWithFlags(&h->pipe[i], cudaStreamNonBlocking));
+    if (!h->ev_pipe) CUDA_TRY(cudaEventCreateWithFlags(&h->ev_pipe, cudaEventDisableTiming));
+
+    rc = b200v_batch_init(h, 0);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev_pipe, h->stream));
+    const int nsteps = policy_is_spiral(c.policy) ? (h->frame_steps / 2) * 2 : h->frame_steps;
+    int nchunks = h->n_frames / min_chunk;
+    if (nchunks > 32) nchunks = 32;
+    const int chunk = (((h->n_frames + nchunks - 1) / nchunks) + 127) / 128 * 128;
+    for (int i = 0; i < b200v_batch::NPIPE; i++) CUDA_TRY(cudaStreamWaitEvent(h->pipe[i], h->ev_pipe, 0));
+    int k = 0;
+    for (int f0 = 0; f0 < h->n_frames; f0 += chunk, k++) {
+        const int cnt = (h->n_frames - f0 < chunk) ? h->n_frames - f0 : chunk;
+        cudaStream_t st = h->pipe[k % b200v_batch::NPIPE];
+        CUDA_TRY(cudaMemcpyAsync((char*)h->d_syms_stage + (size_t)f0 * srow, (const char*)syms + (size_t)f0 * srow,
+                                 (size_t)cnt * srow, cudaMemcpyHostToDevice, st));
+        rc = launch_update_range(h, h->d_syms_stage, srow, nsteps, 0, f0, cnt, st);
+        if (rc) return rc;
+        rc = launch_chainback_range(h, h->d_out_stage, orow, nbits, 0, f0, cnt, st);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(data + (size_t)f0 * orow, h->d_out_stage + (size_t)f0 * orow, (size_t)cnt * orow,
+                                 cudaMemcpyDeviceToHost, st));
+    }
+    for (int i = 0; i < b200v_batch::NPIPE; i++) CUDA_TRY(cudaStreamSynchronize(h->pipe[i]));
+    h->cursor = nsteps;
+    return B200V_OK;
 }
 
 extern "C" int b200v_batch_sync(b200v_batch* h) {

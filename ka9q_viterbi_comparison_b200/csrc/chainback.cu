@@ -13,8 +13,9 @@ namespace {
 
 template <int LAYOUT>
 __global__ void chainback_kernel(const ChainbackArgs a) {
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= a.n_frames) return;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.count) return;
+    const int f = a.frame0 + idx;
     const int K = a.c.K;
     const DecisionReader<LAYOUT> rd(a, f);   // frame-major layouts only
     uint8_t* out = a.out + (size_t)f * a.out_stride;
@@ -58,8 +59,9 @@ __global__ void chainback_kernel(const ChainbackArgs a) {
 __global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a) {
     __shared__ uint8_t tab[k7::NB * k7::S];
     fill_k7_table(tab);
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= a.n_frames) return;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.count) return;
+    const int f = a.frame0 + idx;
     constexpr int K = 7, CHUNK = 16;
     const DecisionReader<DL_K7_INTERLEAVED> rd(a, f, tab);
     uint8_t* out = a.out + (size_t)f * a.out_stride;
@@ -89,9 +91,9 @@ __global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a
 }  // namespace
 
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
-    if (a.n_frames <= 0) return cudaSuccess;
+    if (a.count <= 0) return cudaSuccess;
     const int threads = 128;
-    const int blocks = (a.n_frames + threads - 1) / threads;
+    const int blocks = (a.count + threads - 1) / threads;
     switch (a.layout) {
     case DL_BALLOT_FRAME_MAJOR: chainback_kernel<DL_BALLOT_FRAME_MAJOR><<<blocks, threads, 0, st>>>(a); break;
     case DL_K7_INTERLEAVED: chainback_k7_kernel<<<blocks, threads, 0, st>>>(a); break;

@@ -19,6 +19,7 @@ struct GenericArgs {
     uint16_t* metrics;          // device; [n_frames][S] raw 16-bit (u8 policies zero-extended)
     const uint8_t* cw;          // device; [S/2] code word per butterfly
     int n_frames;
+    int frame0, count;          // this launch works on frames [frame0, frame0 + count)
 };
 struct GenericPlan { int threads_per_frame, frames_per_block, smem_bytes; };
 GenericPlan generic_plan(const CodecParams& c);
@@ -32,14 +33,14 @@ cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecPara
 bool k7_supported(const CodecParams& c);
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          cudaStream_t st);
+                          int frame0, int count, cudaStream_t st);
 
 // ---- group kernels for K=9 / K=15 (acs_grp.cu): decisions as one u64 per (row, frame, thread of the frame) ----
 bool grp_supported(const CodecParams& c);
 int grp_threads_per_frame(const CodecParams& c);
 cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                           cudaStream_t st);
+                           int frame0, int count, cudaStream_t st);
 
 // ---- K=24 (acs_k24.cu): one launch per trellis step, ping-pong metric buffers, canonical decision rows ----
 cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
@@ -54,6 +55,7 @@ struct ChainbackArgs {
     int dec_rows, row_words;    // DL_BALLOT_FRAME_MAJOR geometry
     const uint8_t* row_phase;   // DL_K7_INTERLEAVED / DL_GRP_INTERLEAVED: phase of the step that wrote each row
     int n_frames;
+    int frame0, count;          // this launch works on frames [frame0, frame0 + count)
     const uint16_t* metrics;    // for the KA9Q615 return value
     uint8_t* out;               // device; frame f at out + f*out_stride
     size_t out_stride;

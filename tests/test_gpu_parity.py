@@ -371,3 +371,35 @@ def test_k24_renormalisation_and_streaming():
                 assert np.array_equal(dec.decisions(f, 0, T), qd), (chunks, f)
                 assert np.array_equal(dec.metrics(f), qm), (chunks, f)
                 assert np.array_equal(out[f], qo), (chunks, f)
+
+
+@pytest.mark.parametrize("name", ["ka9q27", "spiral29", "ka9q29", "wy_sse_u16_k7r2"])
+def test_pipelined_batch_decode_matches_whole_batch_launch(name):
+    """b200v_batch_decode cuts large batches into chunks of frames that flow through several streams (copy /
+    compute overlap); the result must equal init + update + chainback of the whole batch, and the oracle."""
+    import torch
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes, n_frames = 16, 4500            # ragged against the 128-frame chunk rounding
+    nbits = nbytes * 8
+    T = nbits + K - 1
+    sb = np.dtype(o.sym_dtype(c)).itemsize
+    amp_q8, sigma_q8, mean_q8, lo, hi = o.channel_params(c, 0.7)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        d_syms = torch.zeros(n_frames * T * R * sb, dtype=torch.uint8, device="cuda")
+        dec.generate_dev(d_syms, T * R * sb, None, 0, nbits, 77, 0, amp_q8, sigma_q8, mean_q8, lo, hi)
+        dec.sync()
+        syms = d_syms.cpu().numpy().view(o.sym_dtype(c)).reshape(n_frames, T * R)
+        out_pipe = dec.decode(syms, nbits)
+        dec_f = {f: dec.decisions(f, 0, T) for f in (0, 2047, 2048, n_frames - 1)}
+        dec.reset()
+        dec.update(syms)
+        out_whole = dec.chainback(nbits)
+        assert np.array_equal(out_pipe, out_whole)
+        for f, d in dec_f.items():
+            assert np.array_equal(d, dec.decisions(f, 0, T)), f
+            q = o.Oracle(c, T)
+            qo, qd = q.decode(syms[f], nbits)
+            assert np.array_equal(out_pipe[f], qo), f
+            assert np.array_equal(d, qd), f
+            q.close()
