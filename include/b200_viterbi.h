@@ -162,6 +162,20 @@ int b200v_batch_generate_dev(b200v_batch* h, void* d_syms, size_t sym_frame_stri
                              unsigned nbits, uint64_t seed, uint64_t frame0,
                              int amp_q8, int sigma_q8, int mean_q8, int lo, int hi);
 
+/* ---- multi-GPU inside one process (frames are independent; no collective) ----
+ * Shard g of G owns the contiguous frames [g*B/G, (g+1)*B/G). */
+int b200v_shard_range(int n_frames, int n_shards, int shard, int* frame0, int* count);
+typedef struct b200v_sharded b200v_sharded;
+/* One b200v_batch per entry of devices[] (a device may appear more than once), sized for its shard. */
+b200v_sharded* b200v_sharded_create(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
+                                    const int* devices, int n_devices, const b200v_wy_config* wy_config);
+void b200v_sharded_destroy(b200v_sharded* s);
+int b200v_sharded_num_shards(const b200v_sharded* s);
+int b200v_sharded_shard(const b200v_sharded* s, int shard, int* frame0, int* count);
+/* b200v_batch_decode of every shard, one host thread per shard, each writing its slice of `data`. */
+int b200v_sharded_decode(b200v_sharded* s, const void* syms, uint8_t* data, unsigned nbits);
+const char* b200v_sharded_last_error(const b200v_sharded* s);
+
 /* ---- device / pinned-host memory helpers (so a C host needs nothing but this library) ---- */
 void* b200v_device_alloc(int device, size_t bytes);
 void  b200v_device_free(int device, void* p);

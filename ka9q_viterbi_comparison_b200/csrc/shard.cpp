@@ -1,0 +1,91 @@
+// shard.cpp -- multi-GPU decode inside one process: frames are independent, so a batch is cut into
+// contiguous frame ranges, one per device, each decoded by its own instance on its own host thread. There is no
+// exchange step and therefore no collective; the host "concatenates" by letting every device write its slice of
+// the caller's output buffer. (bench.py's multi-GPU runs use one process per GPU instead and shard the same way.)
+#include "../../include/b200_viterbi.h"
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <thread>
+#include <vector>
+
+extern "C" int b200v_shard_range(int n_frames, int n_shards, int shard, int* frame0, int* count) {
+    if (n_frames < 0 || n_shards <= 0 || shard < 0 || shard >= n_shards || !frame0 || !count) return B200V_ERR_ARG;
+    // contiguous ranges [g*B/G, (g+1)*B/G): sizes differ by at most one frame
+    const long long lo = (long long)shard * n_frames / n_shards, hi = (long long)(shard + 1) * n_frames / n_shards;
+    *frame0 = (int)lo;
+    *count = (int)(hi - lo);
+    return B200V_OK;
+}
+
+struct b200v_sharded {
+    int n_frames = 0, frame_steps = 0, sym_row = 0;
+    std::vector<b200v_batch*> inst;
+    std::vector<int> frame0, count;
+    std::string error;
+};
+
+extern "C" b200v_sharded* b200v_sharded_create(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
+                                               const int* devices, int n_devices, const b200v_wy_config* wy_config) {
+    if (!devices || n_devices <= 0 || n_frames <= 0) return nullptr;
+    b200v_sharded* s = new (std::nothrow) b200v_sharded();
+    if (!s) return nullptr;
+    s->n_frames = n_frames; s->frame_steps = frame_steps;
+    for (int g = 0; g < n_devices; g++) {
+        int f0 = 0, cnt = 0;
+        b200v_shard_range(n_frames, n_devices, g, &f0, &cnt);
+        b200v_batch* h = cnt > 0 ? b200v_batch_create(codec, K, R, poly, frame_steps, cnt, devices[g], wy_config) : nullptr;
+        if (cnt > 0 && !h) {
+            for (b200v_batch* p : s->inst) b200v_batch_destroy(p);
+            delete s;
+            return nullptr;           // b200v_last_error() holds the reason
+        }
+        s->inst.push_back(h); s->frame0.push_back(f0); s->count.push_back(cnt);
+    }
+    int k = 0, r = 0;
+    b200v_codec_shape(codec, &k, &r);
+    s->sym_row = frame_steps * (r ? r : R) * b200v_codec_symbol_bytes(codec);
+    return s;
+}
+
+extern "C" void b200v_sharded_destroy(b200v_sharded* s) {
+    if (!s) return;
+    for (b200v_batch* p : s->inst) b200v_batch_destroy(p);
+    delete s;
+}
+
+extern "C" int b200v_sharded_num_shards(const b200v_sharded* s) { return s ? (int)s->inst.size() : 0; }
+
+extern "C" int b200v_sharded_shard(const b200v_sharded* s, int shard, int* frame0, int* count) {
+    if (!s || shard < 0 || shard >= (int)s->inst.size()) return B200V_ERR_ARG;
+    if (frame0) *frame0 = s->frame0[(size_t)shard];
+    if (count) *count = s->count[(size_t)shard];
+    return B200V_OK;
+}
+
+extern "C" const char* b200v_sharded_last_error(const b200v_sharded* s) { return s ? s->error.c_str() : ""; }
+
+// init + update + chainback of every shard from host buffers; syms [n_frames][frame_steps*R], data
+// [n_frames][(nbits+7)/8], densely packed. Returns the first failing shard's status.
+extern "C" int b200v_sharded_decode(b200v_sharded* s, const void* syms, uint8_t* data, unsigned nbits) {
+    if (!s || !syms || (!data && nbits)) return B200V_ERR_ARG;
+    const size_t orow = (nbits + 7) / 8;
+    const size_t n = s->inst.size();
+    std::vector<int> rc(n, B200V_OK);
+    std::vector<std::string> msg(n);
+    std::vector<std::thread> th;
+    for (size_t g = 0; g < n; g++) {
+        if (!s->inst[g]) continue;
+        th.emplace_back([&, g]() {
+            rc[g] = b200v_batch_decode(s->inst[g], (const char*)syms + (size_t)s->frame0[g] * (size_t)s->sym_row,
+                                       data + (size_t)s->frame0[g] * orow, nbits);
+            if (rc[g] != B200V_OK) msg[g] = b200v_last_error();      // thread-local in the library
+        });
+    }
+    for (std::thread& t : th) t.join();
+    for (size_t g = 0; g < n; g++)
+        if (rc[g] != B200V_OK) { s->error = "shard " + std::to_string(g) + ": " + msg[g]; return rc[g]; }
+    return B200V_OK;
+}

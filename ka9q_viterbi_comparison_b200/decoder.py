@@ -90,6 +90,13 @@ def load_library():
         "b200v_batch_last_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "b200v_batch_launch_count": (C.c_longlong, [vp]),
         "b200v_batch_generate_dev": (i32, [vp, vp, sz, vp, sz, u32, u64, u64, i32, i32, i32, i32, i32]),
+        "b200v_shard_range": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
+        "b200v_sharded_create": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(WyConfig)]),
+        "b200v_sharded_destroy": (None, [vp]),
+        "b200v_sharded_num_shards": (i32, [vp]),
+        "b200v_sharded_shard": (i32, [vp, i32, C.POINTER(i32), C.POINTER(i32)]),
+        "b200v_sharded_decode": (i32, [vp, vp, vp, u32]),
+        "b200v_sharded_last_error": (C.c_char_p, [vp]),
         "b200v_device_alloc": (vp, [i32, sz]),
         "b200v_device_free": (None, [i32, vp]),
         "b200v_host_alloc_pinned": (vp, [sz]),
@@ -112,7 +119,9 @@ EXPORTED_SYMBOLS = [
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
     "b200v_batch_chainback_results", "b200v_batch_decode", "b200v_batch_sync", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
-    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_device_alloc", "b200v_device_free",
+    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_shard_range", "b200v_sharded_create",
+    "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
+    "b200v_sharded_last_error", "b200v_device_alloc", "b200v_device_free",
     "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
 ]
 
@@ -261,6 +270,64 @@ class BatchDecoder:
             self.close()
         except Exception:
             pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+def shard_range(n_frames, n_shards, shard):
+    """Contiguous frame range [frame0, frame0 + count) of shard `shard` of `n_shards`."""
+    f0, cnt = C.c_int(), C.c_int()
+    rc = load_library().b200v_shard_range(n_frames, n_shards, shard, C.byref(f0), C.byref(cnt))
+    if rc != 0:
+        raise ValueError(f"bad shard arguments ({n_frames}, {n_shards}, {shard})")
+    return f0.value, cnt.value
+
+
+class ShardedDecoder:
+    """One batch instance per device inside this process (b200v_sharded_*): frames are cut into contiguous
+    ranges, each decoded on its device by its own host thread; no collective."""
+
+    def __init__(self, codec, frame_steps, n_frames, devices, K=0, R=0, poly=None):
+        self.lib = load_library()
+        if isinstance(codec, str):
+            codec = CODEC_BY_NAME[codec]
+        k, r = C.c_int(), C.c_int()
+        self.lib.b200v_codec_shape(codec, C.byref(k), C.byref(r))
+        self.K, self.R = k.value or K, r.value or R
+        poly = list(poly if poly is not None else STANDARD_POLYS[(self.K, self.R)])
+        self.codec, self.n_frames, self.frame_steps = codec, n_frames, frame_steps
+        self.sym_dtype = symbol_dtype(codec)
+        devs = (C.c_int * len(devices))(*devices)
+        self.h = self.lib.b200v_sharded_create(codec, self.K, self.R, (C.c_int * len(poly))(*poly), frame_steps,
+                                               n_frames, devs, len(devices), None)
+        if not self.h:
+            raise B200ViterbiError(f"b200v_sharded_create failed: {self.lib.b200v_last_error().decode()}")
+
+    def shards(self):
+        out = []
+        f0, cnt = C.c_int(), C.c_int()
+        for g in range(self.lib.b200v_sharded_num_shards(self.h)):
+            self.lib.b200v_sharded_shard(self.h, g, C.byref(f0), C.byref(cnt))
+            out.append((f0.value, cnt.value))
+        return out
+
+    def decode(self, syms, nbits):
+        syms = np.ascontiguousarray(syms, dtype=self.sym_dtype).reshape(self.n_frames, -1)
+        assert syms.shape[1] == self.frame_steps * self.R
+        out = np.zeros((self.n_frames, (nbits + 7) // 8), dtype=np.uint8)
+        rc = self.lib.b200v_sharded_decode(self.h, syms.ctypes.data, out.ctypes.data, nbits)
+        if rc != 0:
+            raise B200ViterbiError(f"b200v error {rc}: {self.lib.b200v_sharded_last_error(self.h).decode()}")
+        return out
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200v_sharded_destroy(self.h)
+            self.h = None
 
     def __enter__(self):
         return self
