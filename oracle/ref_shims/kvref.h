@@ -48,3 +48,14 @@ void kvref_wy_set_config_kind(int kind);
 #ifdef __cplusplus
 }
 #endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+/* bench.py's CPU arm: decode a pool of frames in a C loop for `seconds` (see registry.cpp). */
+double kvref_time_decode(const kvref_vtable* vt, void* h, const void* syms_pool, int n_pool,
+                         size_t frame_stride_bytes, int T, unsigned nbits, double seconds,
+                         long long* frames_done, uint8_t* out);
+#ifdef __cplusplus
+}
+#endif

@@ -20,3 +20,27 @@ extern "C" const kvref_vtable* kvref_find(const char* name) {
     for (int i = 0; i < kvref_count(); i++) if (!strcmp(g_all[i]->name, name)) return g_all[i];
     return 0;
 }
+
+/* Timed decode loop for bench.py's CPU arm: init + update(T steps) + chainback(nbits) over a pool of frames,
+ * repeated until `seconds` have elapsed. Runs entirely in C so that one Python thread per core measures the
+ * reference decoder and not the interpreter. Returns the elapsed seconds; *frames_done = frames decoded. */
+#include <chrono>
+extern "C" double kvref_time_decode(const kvref_vtable* vt, void* h, const void* syms_pool, int n_pool,
+                                    size_t frame_stride_bytes, int T, unsigned nbits, double seconds,
+                                    long long* frames_done, uint8_t* out) {
+    using clk = std::chrono::steady_clock;
+    const clk::time_point t0 = clk::now();
+    long long n = 0;
+    double dt = 0.0;
+    do {
+        for (int f = 0; f < n_pool; f++) {
+            vt->init(h, 0);
+            vt->update(h, (const char*)syms_pool + (size_t)f * frame_stride_bytes, T);
+            vt->chainback(h, out, nbits, 0);
+            n++;
+        }
+        dt = std::chrono::duration<double>(clk::now() - t0).count();
+    } while (dt < seconds);
+    if (frames_done) *frames_done = n;
+    return dt;
+}

@@ -171,6 +171,10 @@ def ref_lib():
         lib.kvref_count.restype = C.c_int
         lib.kvref_at.restype = C.POINTER(_KvrefVtable)
         lib.kvref_at.argtypes = [C.c_int]
+        if hasattr(lib, "kvref_time_decode"):
+            lib.kvref_time_decode.restype = C.c_double
+            lib.kvref_time_decode.argtypes = [C.POINTER(_KvrefVtable), C.c_void_p, C.c_void_p, C.c_int, C.c_size_t,
+                                              C.c_int, C.c_uint, C.c_double, C.POINTER(C.c_longlong), C.c_void_p]
         _ref = lib
     return _ref
 
@@ -216,6 +220,16 @@ class Ref(_Decoder):
         out = np.zeros(self.S, dtype=metric_dtype(self.codec))
         self.vt.get_metrics(self.h, out.ctypes.data)
         return out
+
+    def time_decode(self, pool, T, nbits, seconds):
+        """Decode the frames of `pool` ([n][T*R] symbols) in a C loop for ~`seconds` (GIL released).
+        Returns (frames decoded, elapsed seconds)."""
+        pool = np.ascontiguousarray(pool, dtype=sym_dtype(self.codec))
+        out = np.zeros((nbits + 7) // 8 + 8, dtype=np.uint8)
+        n = C.c_longlong(0)
+        dt = ref_lib().kvref_time_decode(self.vt, self.h, pool.ctypes.data, pool.shape[0], pool.strides[0], T, nbits,
+                                         seconds, C.byref(n), out.ctypes.data)
+        return n.value, dt
 
     def close(self):
         if getattr(self, "h", None):
