@@ -98,33 +98,45 @@ struct K7Args {
     int n_frames;
     int frame0, count;             // frames [frame0, frame0 + count) of the n_frames-wide layout
     int C, thr, soft_hi, soft_lo;
+    int one, neg1;                 // 1 and -1, opaque to ptxas: multipliers that keep plain adds on the FMA pipe
 };
 
 // ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
 template <int POLICY, class CODE, int P, int KK>
 struct PairLoop {
     __device__ __forceinline__ static void run(uint32_t (&w)[NW], const uint32_t* W, const uint32_t* Wc,
-                                               uint32_t clamp, uint32_t& acc0, uint32_t& acc1) {
+                                               uint32_t clamp, const K7Args& a, uint32_t& acc0, uint32_t& acc1) {
         constexpr int XB = NB - 2 - P;                         // register-index bit that holds the state MSB
         constexpr int iA = expand_bit(KK, XB), iB = iA | (1 << XB);
         constexpr int c = CODE::cw(logical_of(P, iA << 1));
         const uint32_t A = w[iA], B = w[iB];
-        const uint32_t m0 = Arith<POLICY>::add(A, W[c], clamp), m1 = Arith<POLICY>::add(B, Wc[c], clamp);
-        const uint32_t m2 = Arith<POLICY>::add(A, Wc[c], clamp), m3 = Arith<POLICY>::add(B, W[c], clamp);
         if (Arith<POLICY>::modular) {      // decision = (lo path > hi path), tie -> 0 (viterbi27_sse2.cpp:155-158)
+            const uint32_t m0 = A + W[c], m1 = B + Wc[c], m2 = A + Wc[c], m3 = B + W[c];
             w[iA] = min_acc<KK, 16 + KK, true>(m0, m1, acc0);
             w[iB] = min_acc<KK, 16 + KK, true>(m2, m3, acc1);
-        } else {                           // decision = (min == hi path), tie -> 1 (spiral27.cpp:178-181)
-            w[iA] = min_acc<KK, 16 + KK, false>(m1, m0, acc0);
-            w[iB] = min_acc<KK, 16 + KK, false>(m3, m2, acc1);
+        } else {
+            // Saturating policies. Only the hi-path candidates need the clamp (the survivor is min(lo, hi) <= hi
+            // <= clamp, and a doubly saturated butterfly still decides "hi" because hi == clamp); the lo-path adds
+            // are plain adds on the FMA pipe. decision = (min == hi path) = (lo - hi >= 0), tie -> 1
+            // (spiral27.cpp:178-181): bit 15 of each lane of lo + 0x8000 - hi (|lo - hi| < 2^15), also on the FMA
+            // pipe; the two bits are shifted into the decision word (pair KK ends at bits KK / 16+KK after the
+            // 16 pairs). No predicates: ptxas spilled them in the predicated form of this loop.
+            const uint32_t m0 = add_fma(A, (uint32_t)a.one, W[c]), m1 = __viaddmin_u16x2(B, Wc[c], clamp);
+            const uint32_t m2 = add_fma(A, (uint32_t)a.one, Wc[c]), m3 = __viaddmin_u16x2(B, W[c], clamp);
+            const uint32_t x0 = add_fma(m1, (uint32_t)a.neg1, add_fma(m0, (uint32_t)a.one, 0x80008000u));
+            const uint32_t x1 = add_fma(m3, (uint32_t)a.neg1, add_fma(m2, (uint32_t)a.one, 0x80008000u));
+            w[iA] = __vminu2(m1, m0);
+            w[iB] = __vminu2(m3, m2);
+            acc0 = (acc0 >> 1) | (x0 & 0x80008000u);
+            acc1 = (acc1 >> 1) | (x1 & 0x80008000u);
         }
-        PairLoop<POLICY, CODE, P, KK + 1>::run(w, W, Wc, clamp, acc0, acc1);
+        PairLoop<POLICY, CODE, P, KK + 1>::run(w, W, Wc, clamp, a, acc0, acc1);
     }
 };
 template <int POLICY, class CODE, int P>
 struct PairLoop<POLICY, CODE, P, 16> {
     __device__ __forceinline__ static void run(uint32_t (&)[NW], const uint32_t*, const uint32_t*, uint32_t,
-                                               uint32_t&, uint32_t&) {}
+                                               const K7Args&, uint32_t&, uint32_t&) {}
 };
 
 // last phase: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
@@ -140,7 +152,10 @@ struct InRegLoop {
         const uint32_t hi_paths = __byte_perm(mb, ma, 0x7632);               // (m1, m3)
         uint32_t& acc = (I < 16) ? acc0 : acc1;
         if (Arith<POLICY>::modular) w[I] = min_acc<(I & 15), 16 + (I & 15), true>(lo_paths, hi_paths, acc);
-        else w[I] = min_acc<(I & 15), 16 + (I & 15), false>(hi_paths, lo_paths, acc);
+        else {      // same arithmetic decision as PairLoop; registers 0..15 fill acc0, 16..31 fill acc1, in order
+            w[I] = __vminu2(hi_paths, lo_paths);
+            acc = (acc >> 1) | ((lo_paths + 0x80008000u - hi_paths) & 0x80008000u);
+        }
         InRegLoop<POLICY, CODE, I + 1>::run(w, bm, cm, clamp, acc0, acc1);
     }
 };
@@ -165,7 +180,7 @@ __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7
         uint32_t W[NCW], Wc[NCW];
 #pragma unroll
         for (int c = 0; c < NCW; c++) { W[c] = pack2(bm[c], bm[c ^ DELTA]); Wc[c] = pack2(cm[c], cm[c ^ DELTA]); }
-        PairLoop<POLICY, CODE, P, 0>::run(w, W, Wc, clamp, acc0, acc1);
+        PairLoop<POLICY, CODE, P, 0>::run(w, W, Wc, clamp, a, acc0, acc1);
     } else {
         // in-register butterflies: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
         InRegLoop<POLICY, CODE, 0>::run(w, bm, cm, clamp, acc0, acc1);
@@ -274,8 +289,8 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
         drow[3 * dstride] = d3; drow[4 * dstride] = d4; drow[5 * dstride] = d5;
         drow += 6 * dstride;
         cur = nxt;
-        // keep the 16-bit lanes from overflowing: every 64 periods rebase (uniform across the warp)
-        if ((pd & 63) == 63) {
+        // keep the 16-bit lanes from overflowing: every 16 periods rebase (uniform across the warp)
+        if ((pd & 15) == 15) {
             if (Arith<POLICY>::modular) {
                 // subtract a multiple of 256 (keeps U mod 256): floor(min/256)*256 - 256
                 uint32_t mn = w[0];
@@ -373,6 +388,7 @@ cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_str
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
+    a.one = 1; a.neg1 = -1;
     switch (k7::find_instance(c)) {
     case 0: return k7::launch_one<P_KA9Q_U8_MOD, k7::CodeK7R2>(a, st);
     case 1: return k7::launch_one<P_SPIRAL_R2, k7::CodeK7R2>(a, st);
