@@ -33,6 +33,8 @@ def parse():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--codec", default="ka9q27")
+    p.add_argument("--K", type=int, default=7, help="constraint length (wy_u8 / wy_u16 only)")
+    p.add_argument("--R", type=int, default=2, help="code rate 1/R (wy_u8 / wy_u16 only)")
     p.add_argument("--frames", type=int, default=0, help="frames per GPU (default: 1 Mi for K<=9, 8192 for K=15)")
     p.add_argument("--frame-bits", type=int, default=2048)
     p.add_argument("--sigma", type=float, default=0.7, help="channel noise (0 = main.cpp's noiseless symbols)")
@@ -45,18 +47,29 @@ def parse():
 
 # oracle registry name (CPU reference arm) for each product codec
 REF_NAME = {"ka9q27": "ka9q27", "ka9q29": "ka9q29", "ka9q615": "ka9q615", "spiral27": "spiral27",
-            "spiral29": "spiral29", "spiral47": "spiral47", "spiral49": "spiral49", "spiral615": "spiral615"}
+            "spiral29": "spiral29", "spiral47": "spiral47", "spiral49": "spiral49", "spiral615": "spiral615",
+            "ka9q224": "ka9q224"}
 
 
-def codec_shape(codec):
+def codec_shape(codec, K=7, R=2):
+    """(K, R) of a fixed codec; the williamyang families take them from --K / --R."""
     import ka9q_viterbi_comparison_b200 as kv
     k, r = C.c_int(), C.c_int()
     kv.load_library().b200v_codec_shape(kv.CODEC_BY_NAME[codec], C.byref(k), C.byref(r))
-    return k.value, r.value
+    return (k.value, r.value) if k.value else (K, R)
+
+
+def ref_name(codec, K, R):
+    """oracle registry name of the reference decoder that matches a product codec"""
+    if codec == "wy_u8":
+        return f"wy_avx_u8_k{K}r{R}"
+    if codec == "wy_u16":
+        return f"wy_avx_u16_k{K}r{R}"
+    return REF_NAME[codec]
 
 
 def default_frames(K):
-    return 1 << 20 if K <= 9 else 8192
+    return 1 << 20 if K <= 9 else 8192 if K <= 16 else 16
 
 
 def channel_params(lo, hi, sigma):
@@ -113,12 +126,12 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------
 # CPU reference arm: the reference's own decoder on the host cores (oracle/_ref, else the oracle port)
 # ---------------------------------------------------------------------------------------------------
-def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None):
+def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None, K=7, R=2):
     """Decode frames of `frame_bits` with one decoder instance per host thread for ~`seconds`.
     Returns (Mbit/s aggregate, threads, kind, sample description)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle as o
-    name = REF_NAME[codec]
+    name = ref_name(codec, K, R)
     c = o.codec_by_name(name)
     nbytes = frame_bits // 8
     T = frame_bits + c.K - 1
@@ -163,12 +176,12 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    K, R = codec_shape(args.codec)
+    K, R = codec_shape(args.codec, args.K, args.R)
     per_step = max(1.0, min(args.cpu_seconds, 240.0 / max(1, args.steps + args.warmup)))
     vals = []
     info = None
     for i in range(args.warmup + args.steps):
-        v, cores, kind, sample = cpu_reference_rate(args.codec, args.frame_bits, args.sigma, per_step)
+        v, cores, kind, sample = cpu_reference_rate(args.codec, args.frame_bits, args.sigma, per_step, K=K, R=R)
         if i >= args.warmup:
             vals.append(v)
             info = (cores, kind, sample)
@@ -206,16 +219,16 @@ def run_b200_arm(args):
     dev = torch.device("cuda", local)
 
     codec = kv.CODEC_BY_NAME[args.codec]
-    K, R = codec_shape(args.codec)
+    K, R = codec_shape(args.codec, args.K, args.R)
     S = 1 << (K - 1)
     nbits = args.frame_bits
     T = nbits + K - 1
     frames = args.frames or default_frames(K)
     sym_bytes = kv.load_library().b200v_codec_symbol_bytes(codec)
-    lo, hi = {1: (0, 255)}.get(sym_bytes, (-127, 127))
+    lo, hi = (-3, 3) if args.codec == "wy_u8" else {1: (0, 255)}.get(sym_bytes, (-127, 127))
     srow, orow = T * R * sym_bytes, nbits // 8
 
-    dec = kv.BatchDecoder(codec, T, frames, device=local)
+    dec = kv.BatchDecoder(codec, T, frames, K=K, R=R, device=local)
     if args.variant:
         dec.set_variant(args.variant)
     # a non-default torch stream: the library treats a NULL stream handle as "use the instance's own stream",
@@ -329,8 +342,8 @@ def run_b200_arm(args):
                 "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "note": "4*S integer lane-ops per trellis step"}}
 
     cpu = None
-    if not args.no_cpu_baseline and args.codec in REF_NAME:
-        v, cores, kind, sample = cpu_reference_rate(args.codec, nbits, args.sigma, args.cpu_seconds)
+    if not args.no_cpu_baseline:
+        v, cores, kind, sample = cpu_reference_rate(args.codec, nbits, args.sigma, args.cpu_seconds, K=K, R=R)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
 
     line = {
