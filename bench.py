@@ -40,6 +40,7 @@ def parse():
     p.add_argument("--sigma", type=float, default=0.7, help="channel noise (0 = main.cpp's noiseless symbols)")
     p.add_argument("--variant", type=int, default=0, help="kernel family: 0 auto, 1 generic, 2 specialised")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--unfused", action="store_true", help="time init/update/chainback as three calls instead of b200v_batch_decode_dev")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--cpu-seconds", type=float, default=6.0)
     return p.parse_args()
@@ -244,10 +245,16 @@ def run_b200_arm(args):
     dec.generate_dev(d_syms, srow, d_data, orow, nbits, 0xB200, rank * frames, amp_q8, sigma_q8, mean_q8, lo, hi)
     torch.cuda.synchronize()
 
-    def step():
+    def step_calls():
         dec.reset()
         dec.update_dev(d_syms, srow, T)
         dec.chainback_dev(d_out, orow, nbits)
+
+    def step():
+        if args.unfused:
+            step_calls()
+        else:
+            dec.decode_dev(d_syms, srow, d_out, orow, nbits)
 
     def barrier():
         torch.cuda.synchronize()
@@ -273,7 +280,7 @@ def run_b200_arm(args):
     launches = dec.launch_count - launches0
     # per-kernel device time (CUDA events on the launching stream, recorded inside the library)
     for _ in range(3):
-        step()
+        step_calls()
         u, c = dec.last_kernel_ms()
         upd_ms.append(u)
         cb_ms.append(c)
@@ -351,7 +358,7 @@ def run_b200_arm(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8" if sym_bytes == 1 else "u16", "data": "synthetic",
         "config": {"workload": f"{args.codec} K={K} r=1/{R}: {frames} frames x {nbits} bits per GPU",
-                   "sigma": args.sigma, "kernel_variant": dec.variant, "l2": "inputs larger than L2"
+                   "sigma": args.sigma, "kernel_variant": dec.variant, "entry": "calls" if args.unfused else "decode_dev", "l2": "inputs larger than L2"
                    if frames * srow > 126e6 else "inputs smaller than L2", "sample_ber": ber},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
     }

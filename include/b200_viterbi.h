@@ -132,6 +132,11 @@ int b200v_batch_chainback_results(b200v_batch* h, int* results);
  * syms: [n_frames][frame_steps*R] symbols, data: [n_frames][(nbits+7)/8] bytes, both densely packed. */
 int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits);
 
+/* The same with symbols and output already in HBM (device pointers, frame strides in bytes). Asynchronous; ordered
+ * on the instance's stream. */
+int b200v_batch_decode_dev(b200v_batch* h, const void* d_syms, size_t sym_stride_bytes, uint8_t* d_data,
+                           size_t out_stride_bytes, unsigned nbits);
+
 /* Wait for everything queued on the instance's stream. */
 int b200v_batch_sync(b200v_batch* h);
 

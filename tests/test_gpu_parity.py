@@ -380,7 +380,7 @@ def test_pipelined_batch_decode_matches_whole_batch_launch(name):
     import torch
     codec, K, R = CASES[name]
     c = o.codec_by_name(name)
-    nbytes, n_frames = 16, 4500            # ragged against the 128-frame chunk rounding
+    nbytes, n_frames = 16, 33000           # ragged against the 128-frame chunk rounding; several chunks in both entries
     nbits = nbytes * 8
     T = nbits + K - 1
     sb = np.dtype(o.sym_dtype(c)).itemsize
@@ -396,6 +396,11 @@ def test_pipelined_batch_decode_matches_whole_batch_launch(name):
         dec.update(syms)
         out_whole = dec.chainback(nbits)
         assert np.array_equal(out_pipe, out_whole)
+        # device-pointer entry (chunks over internal streams, ordered on the instance's stream)
+        d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
+        dec.decode_dev(d_syms, T * R * sb, d_out, nbytes, nbits)
+        dec.sync()
+        assert np.array_equal(d_out.cpu().numpy().reshape(n_frames, nbytes), out_whole)
         for f, d in dec_f.items():
             assert np.array_equal(d, dec.decisions(f, 0, T)), f
             q = o.Oracle(c, T)
