@@ -53,8 +53,20 @@ struct Cfg {
     static constexpr int ESHIFT = modular ? 4 : 3;              // table entry: {W, Wc} or {W, Wc, X0, X1}
     static constexpr int SUBTAB = NCW << ESHIFT;                // one step's table
     static constexpr int TAB_BYTES = 2 * NL * SUBTAB;           // two groups (double buffer) x five steps
+    // Several frames per warp (K=9) read their own tables with one LDS: frame f's tables must sit in other banks
+    // than frame f+1's. Step tables narrower than 128 B: pad the per-frame stride so that consecutive frames are
+    // one step-table apart modulo the 32 banks. 128-byte step tables fill all banks: frames permute their entries
+    // instead (frame_perm below).
+    static constexpr int tab_stride() {
+        if (FPB == 1 || SUBTAB >= 128) return TAB_BYTES;
+        int st = TAB_BYTES;
+        while ((st / 4) % 32 != (SUBTAB / 4) % 32) st += SUBTAB;
+        return st;
+    }
+    static constexpr int TAB_STRIDE = tab_stride();
+    static constexpr bool PERMUTE = (FPB > 1 && SUBTAB >= 128);
     static constexpr int RED_WORDS = 2 * 16;                    // block reduction scratch (TPF >= 32)
-    static constexpr int SMEM = FPB * TAB_BYTES + FPB * MET_STRIDE + RED_WORDS * 4;
+    static constexpr int SMEM = FPB * TAB_STRIDE + FPB * MET_STRIDE + RED_WORDS * 4;
     static constexpr bool s16 = (POLICY == P_KA9Q_S16_615);
     static constexpr bool strict = PolicyTraits<POLICY>::renorm_strict;
     static constexpr int TOP = (s16 || POLICY == P_WY_U16) ? 65535 : 255;
@@ -267,12 +279,121 @@ __device__ __forceinline__ void exchange_load(uint32_t (&w)[NREG], uint32_t met_
     }
 }
 
+// ---- per-frame entry permutation of 128-byte step tables (K=9 r=1/4) -----------------------------------------
+// The four threads of a frame read entries c ^ cx(tx), a coset of V_p = span(cw2(1 << (p+2)), cw2(1 << (p+3))).
+// Frame f of a half-warp (4 frames = one LDS.64 transaction) stores entry c at position c ^ H_p(f & 3), where
+// H_p(.) runs over coset representatives of V_p, so the 16 lanes of the transaction hit 16 different entries.
+__host__ __device__ constexpr unsigned gf2_reduce(unsigned v, unsigned b0, unsigned b1, unsigned b2, unsigned b3) {
+    for (int it = 0; it < 8; it++) {
+        if (b0 && (v ^ b0) < v) v ^= b0;
+        if (b1 && (v ^ b1) < v) v ^= b1;
+        if (b2 && (v ^ b2) < v) v ^= b2;
+        if (b3 && (v ^ b3) < v) v ^= b3;
+    }
+    return v;
+}
+// which-th (0 or 1) unit vector that extends {g1, g2} towards a basis of GF(2)^R
+__host__ __device__ constexpr unsigned gf2_complement(unsigned g1, unsigned g2, int R, int which) {
+    unsigned b0 = g1, b1 = gf2_reduce(g2, g1, 0, 0, 0), b2 = 0, b3 = 0;
+    int found = 0;
+    for (int k = 0; k < R; k++) {
+        const unsigned r = gf2_reduce(1u << k, b0, b1, b2, b3);
+        if (r) {
+            if (found == which) return 1u << k;
+            if (found == 0) b2 = r; else b3 = r;
+            found++;
+        }
+    }
+    return 0;
+}
+template <class CODE>
+__host__ __device__ constexpr unsigned frame_perm(int p, int f) {
+    const unsigned g1 = CODE::cw2(1u << (p + 2)), g2 = CODE::cw2(1u << (p + 3));
+    return ((f & 1) ? gf2_complement(g1, g2, CODE::R, 0) : 0u) ^ ((f & 2) ? gf2_complement(g1, g2, CODE::R, 1) : 0u);
+}
+
+// ---- per-symbol costs: every policy's branch metric is post(sum_i v_i[c_i]) (same formulas as bm_eval) -----
+template <int POLICY>
+__device__ __forceinline__ void symbol_costs(int sym, const GrpArgs& a, int& v0, int& v1) {
+    if (POLICY == P_WY_U8) {
+        v0 = abs(clamp_i(a.soft_lo - sym, -128, 127));
+        v1 = abs(clamp_i(a.soft_hi - sym, -128, 127));
+    } else if (POLICY == P_SPIRAL_R4 || POLICY == P_SPIRAL_615) {
+        v0 = (sym >> 2) & 63;
+        v1 = ((sym ^ 255) >> 2) & 63;
+    } else {
+        v0 = sym;
+        v1 = sym ^ 255;
+    }
+}
+template <int POLICY>
+__device__ __forceinline__ int bm_post(int sum) {
+    if (POLICY == P_WY_U8) return min(sum, 255);
+    if (POLICY == P_SPIRAL_R4 || POLICY == P_SPIRAL_615) return (min(sum, 255) >> 2) & 63;
+    if (POLICY == P_SPIRAL_R2) return (((sum + 1) >> 1) >> 2) & 63;
+    if (POLICY == P_KA9Q_U8_MOD) return ((sum + 1) >> 1) >> 4;
+    return sum;
+}
+
+// Cooperative table build for TPF = 4 (K=9): per step, each of the frame's four threads evaluates NCW/4 code
+// words as subset sums of the per-symbol costs, fetches the lane-1 partner (code word ^ D_s) with one shuffle
+// and writes its NCW/4 entries. ~4x fewer instructions than one bm_eval per code word and task.
+template <int POLICY, class CODE, class CF>
+__device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl) {
+    constexpr int R = CF::R, NPT = CF::NCW / 4, LOGN = (NPT == 1 ? 0 : NPT == 2 ? 1 : NPT == 4 ? 2 : NPT == 8 ? 3 : 4);
+    static_assert(CF::TPF == 4 && CF::NCW >= 4 && (1 << LOGN) == NPT, "four threads per frame, NCW/4 code words each");
+    const uint32_t buf = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
+#pragma unroll
+    for (int s = 0; s < NL; s++) {
+        const int t = g * NL + s;
+        if (t >= a.nsteps) break;                       // uniform over the block
+        constexpr int DUMMY = 0; (void)DUMMY;
+        const unsigned D = CODE::cw2(1u << (s + 1));    // compile-time after unrolling
+        const unsigned char* p = sp + (size_t)t * R;
+        int v0[R], v1[R];
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int sym = (POLICY == P_WY_U8) ? (int)(int8_t)__ldg(p + i) : (int)__ldg(p + i);
+            symbol_costs<POLICY>(sym, a, v0[i], v1[i]);
+        }
+        // code words of this thread: c = tx * NPT + j; the two top bits of c come from tx
+        int top = ((tx & 1) ? v1[LOGN] : v0[LOGN]) + ((tx & 2) ? v1[LOGN + 1] : v0[LOGN + 1]);
+        uint32_t X[NPT];                                // (bm, cm) packed; scaled by 256 for the modular policy
+#pragma unroll
+        for (int j = 0; j < NPT; j++) {
+            int sum = top;
+#pragma unroll
+            for (int i = 0; i < LOGN; i++) sum += ((j >> i) & 1) ? v1[i] : v0[i];
+            const int bm = bm_post<POLICY>(sum), cm = max(a.C - bm, 0);
+            X[j] = CF::modular ? pack2((uint32_t)bm << 8, (uint32_t)cm << 8) : pack2((uint32_t)bm, (uint32_t)cm);
+        }
+        const unsigned fp = CF::PERMUTE ? (((fl & 1) ? frame_perm<CODE>(s, 1) : 0u) ^ ((fl & 2) ? frame_perm<CODE>(s, 2) : 0u)) : 0u;
+        const uint32_t st = buf + (uint32_t)s * CF::SUBTAB;
+        const unsigned c0 = (unsigned)(tx * NPT);
+#pragma unroll
+        for (int j = 0; j < NPT; j++) {
+            const int jp = j ^ (int)(D & (NPT - 1));
+            const uint32_t Xd = (D >> LOGN) ? __shfl_xor_sync(0xffffffffu, X[jp], (int)(D >> LOGN)) : X[jp];
+            const uint32_t W = __byte_perm(X[j], Xd, 0x5410), Wc = __byte_perm(X[j], Xd, 0x7632);
+            if (CF::modular)
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(st + (((c0 + j) ^ fp) << 4)), "r"(W), "r"(Wc),
+                             "r"(__vadd2(__vsub2(W, Wc), 0x00010001u)), "r"(__vadd2(__vsub2(Wc, W), 0x00010001u)) : "memory");
+            else
+                sts64(st + (((c0 + j) ^ fp) << 3), W, Wc);
+        }
+    }
+}
+
 // ---- branch-metric tables of one group of five steps ---------------------------------------------------
 // entry (s, c) = { pack(bm[c], bm[c ^ D_s]), pack(cm[c], cm[c ^ D_s]) }, D_s = code-word difference between the
 // two lanes of a register in phase s. One task computes bm of c and c ^ D_s once and writes both entries.
 template <int POLICY, class CODE, class CF>
-__device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx) {
+__device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl) {
     constexpr int R = CF::R, HALF = CF::NCW / 2;
+    if constexpr (CF::TPF == 4 && CF::NCW >= 4) {
+        fill_tables_coop<POLICY, CODE, CF>(a, sp, g, tab_addr, tx, fl);
+        return;
+    }
     const uint32_t buf = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
     for (int e = tx; e < NL * HALF; e += CF::TPF) {
         const int s = e / HALF, idx = e - s * HALF;
@@ -349,10 +470,10 @@ acs_grp_kernel(const GrpArgs a) {
     const bool live = fidx < a.count;
     const int frame = a.frame0 + (live ? fidx : a.count - 1);
 
-    const uint32_t tab_addr = smem_u32(smem) + (uint32_t)fl * CF::TAB_BYTES;
-    unsigned char* met_ptr = smem + CF::FPB * CF::TAB_BYTES + (size_t)fl * CF::MET_STRIDE;
+    const uint32_t tab_addr = smem_u32(smem) + (uint32_t)fl * CF::TAB_STRIDE;
+    unsigned char* met_ptr = smem + CF::FPB * CF::TAB_STRIDE + (size_t)fl * CF::MET_STRIDE;
     const uint32_t met_addr = smem_u32(met_ptr);
-    uint32_t* s_red = reinterpret_cast<uint32_t*>(smem + CF::FPB * CF::TAB_BYTES + CF::FPB * CF::MET_STRIDE);
+    uint32_t* s_red = reinterpret_cast<uint32_t*>(smem + CF::FPB * CF::TAB_STRIDE + CF::FPB * CF::MET_STRIDE);
     int rpar = 0;
 
     if (blockIdx.x == 0)
@@ -390,6 +511,7 @@ acs_grp_kernel(const GrpArgs a) {
         unsigned c = 0;
 #pragma unroll
         for (int i = 0; i < CF::R; i++) c |= (unsigned)(__popc(((unsigned)tx << (p + 2)) & CODE::poly(i)) & 1) << i;
+        if (CF::PERMUTE) c ^= ((fl & 1) ? frame_perm<CODE>(p, 1) : 0u) ^ ((fl & 2) ? frame_perm<CODE>(p, 2) : 0u);
         cx8[p] = c << CF::ESHIFT;
     }
 
@@ -398,13 +520,13 @@ acs_grp_kernel(const GrpArgs a) {
     unsigned long long* drow = a.dec + ((size_t)a.step0 * a.n_frames + frame) * CF::TPF + tx;
 
     const int ngroups = (a.nsteps + NL - 1) / NL;
-    if (ngroups > 0) fill_tables<POLICY, CODE, CF>(a, sp, 0, tab_addr, tx);
+    if (ngroups > 0) fill_tables<POLICY, CODE, CF>(a, sp, 0, tab_addr, tx, fl);
     if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
 
 #pragma unroll 1
     for (int g = 0; g < ngroups; g++) {
         const int nsub = min(NL, a.nsteps - g * NL);
-        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx);
+        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx, fl);
         const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
         step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
         if (nsub > 1) step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);
