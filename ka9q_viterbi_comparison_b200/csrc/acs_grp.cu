@@ -70,6 +70,9 @@ struct Cfg {
     static constexpr bool s16 = (POLICY == P_KA9Q_S16_615);
     static constexpr bool strict = PolicyTraits<POLICY>::renorm_strict;
     static constexpr int TOP = (s16 || POLICY == P_WY_U16) ? 65535 : 255;
+    static constexpr int SB = (POLICY == P_WY_U16) ? 2 : 1;     // bytes per input symbol
+    // rebase the lanes when their minimum exceeds TH: window = TH + metric spread + two branch metrics < 2^16
+    static constexpr unsigned TH = (TOP == 65535) ? 4096u : 16384u;
     static_assert(NXB >= 3, "at least 4 threads per frame");
     static_assert(TPF <= 4 || NXB + 1 >= 10, "exchange swizzle is written for K=9 and K=15");
 };
@@ -86,6 +89,18 @@ struct GrpArgs {
     int one;                       // 1 (a multiplier ptxas cannot fold: keeps the lo-path adds on the FMA pipe)
 };
 
+// symbol i of a step (u8 for ka9q/spiral, int8 / int16 for the williamyang policies)
+template <int POLICY>
+__device__ __forceinline__ int ld_symbol(const unsigned char* step_ptr, int i) {
+    if (POLICY == P_WY_U16) return (int)(int16_t)__ldg(reinterpret_cast<const unsigned short*>(step_ptr) + i);
+    if (POLICY == P_WY_U8) return (int)(int8_t)__ldg(step_ptr + i);
+    return (int)__ldg(step_ptr + i);
+}
+// largest single branch metric the lane window is sized for (wy-u16: api.cu checks the symbols of every update
+// against the range that guarantees it, and routes other inputs to the generic kernel)
+template <int POLICY, int TOP>
+__device__ __forceinline__ int bm_cap(int C) { return TOP == 255 ? 255 : (POLICY == P_WY_U16 ? 2 * C : C); }
+
 // scalar branch metric / complement of code word cw for one step's symbols (same formulas as policy.cuh)
 template <int POLICY, int R>
 __device__ __forceinline__ void bm_eval(unsigned cw, const int* sym, const GrpArgs& a, uint32_t& bm, uint32_t& cm) {
@@ -96,6 +111,14 @@ __device__ __forceinline__ void bm_eval(unsigned cw, const int* sym, const GrpAr
         for (int i = 0; i < R; i++) {
             const int bt = ((cw >> i) & 1u) ? a.soft_hi : a.soft_lo;
             tot = min(tot + abs(clamp_i(bt - sym[i], -128, 127)), 255);
+        }
+        v = tot;
+    } else if (POLICY == P_WY_U16) {
+        int tot = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int bt = ((cw >> i) & 1u) ? a.soft_hi : a.soft_lo;
+            tot = min(tot + abs(clamp_i(bt - sym[i], -32768, 32767)), 65535);
         }
         v = tot;
     } else if (POLICY == P_KA9Q_S16_615) {
@@ -197,13 +220,13 @@ __device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint
     const int thr = a.thr + (CF::s16 ? 32768 : 0);
     const bool need = CF::strict ? (tb0 > thr) : (tb0 >= thr);
     if (need) fs.base = -(int)gmin;
-    if (gmin > 16384u) {       // uniform over the frame
+    if (gmin > CF::TH) {       // uniform over the frame
         const uint32_t sub = gmin * 0x10001u;
 #pragma unroll
         for (int i = 0; i < NREG; i++) w[i] -= sub;      // every lane >= gmin: no borrow between lanes
         fs.base += (int)gmin;
     }
-    set_clamp<POLICY, CF>(fs, CF::TOP == 255 ? 255 : a.C);
+    set_clamp<POLICY, CF>(fs, bm_cap<POLICY, CF::TOP>(a.C));
 }
 
 // ---- butterflies of one step in phase P -------------------------------------------------------------------
@@ -318,6 +341,9 @@ __device__ __forceinline__ void symbol_costs(int sym, const GrpArgs& a, int& v0,
     if (POLICY == P_WY_U8) {
         v0 = abs(clamp_i(a.soft_lo - sym, -128, 127));
         v1 = abs(clamp_i(a.soft_hi - sym, -128, 127));
+    } else if (POLICY == P_WY_U16) {
+        v0 = abs(clamp_i(a.soft_lo - sym, -32768, 32767));
+        v1 = abs(clamp_i(a.soft_hi - sym, -32768, 32767));
     } else if (POLICY == P_SPIRAL_R4 || POLICY == P_SPIRAL_615) {
         v0 = (sym >> 2) & 63;
         v1 = ((sym ^ 255) >> 2) & 63;
@@ -329,6 +355,7 @@ __device__ __forceinline__ void symbol_costs(int sym, const GrpArgs& a, int& v0,
 template <int POLICY>
 __device__ __forceinline__ int bm_post(int sum) {
     if (POLICY == P_WY_U8) return min(sum, 255);
+    if (POLICY == P_WY_U16) return min(sum, 65535);
     if (POLICY == P_SPIRAL_R4 || POLICY == P_SPIRAL_615) return (min(sum, 255) >> 2) & 63;
     if (POLICY == P_SPIRAL_R2) return (((sum + 1) >> 1) >> 2) & 63;
     if (POLICY == P_KA9Q_U8_MOD) return ((sum + 1) >> 1) >> 4;
@@ -349,11 +376,11 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
         if (t >= a.nsteps) break;                       // uniform over the block
         constexpr int DUMMY = 0; (void)DUMMY;
         const unsigned D = CODE::cw2(1u << (s + 1));    // compile-time after unrolling
-        const unsigned char* p = sp + (size_t)t * R;
+        const unsigned char* p = sp + (size_t)t * R * CF::SB;
         int v0[R], v1[R];
 #pragma unroll
         for (int i = 0; i < R; i++) {
-            const int sym = (POLICY == P_WY_U8) ? (int)(int8_t)__ldg(p + i) : (int)__ldg(p + i);
+            const int sym = ld_symbol<POLICY>(p, i);
             symbol_costs<POLICY>(sym, a, v0[i], v1[i]);
         }
         // code words of this thread: c = tx * NPT + j; the two top bits of c come from tx
@@ -404,9 +431,9 @@ __device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned cha
         if (D) { c1 = (unsigned)k7::expand_bit(idx, 31 - __clz(D)); c2 = c1 ^ D; }
         else { c1 = (unsigned)idx; c2 = (unsigned)(idx + HALF); }
         int sym[R];
-        const unsigned char* p = sp + (size_t)t * R;
+        const unsigned char* p = sp + (size_t)t * R * CF::SB;
 #pragma unroll
-        for (int i = 0; i < R; i++) sym[i] = (POLICY == P_WY_U8) ? (int)(int8_t)__ldg(p + i) : (int)__ldg(p + i);
+        for (int i = 0; i < R; i++) sym[i] = ld_symbol<POLICY>(p, i);
         uint32_t b1, m1, b2, m2;
         bm_eval<POLICY, R>(c1, sym, a, b1, m1);
         bm_eval<POLICY, R>(c2, sym, a, b2, m2);
@@ -501,7 +528,7 @@ acs_grp_kernel(const GrpArgs a) {
 #pragma unroll
         for (int i = 0; i < NREG; i++) w[i] -= sub;
         fs.base = (int)gmin;
-        set_clamp<POLICY, CF>(fs, CF::TOP == 255 ? 255 : a.C);
+        set_clamp<POLICY, CF>(fs, bm_cap<POLICY, CF::TOP>(a.C));
     }
 
     // the thread's own contribution to the code word of its butterflies, per phase (byte offset into a table)
@@ -579,20 +606,24 @@ static bool same_code(const CodecParams& c) {
     return true;
 }
 
-enum Instance { I_NONE = -1, I_KA9Q29, I_KA9Q615, I_SPIRAL615, I_WY8_K15R6, I_SPIRAL29, I_WY8_K9R2, I_SPIRAL49, I_WY8_K9R4 };
+enum Instance { I_NONE = -1, I_KA9Q29, I_KA9Q615, I_SPIRAL615, I_WY8_K15R6, I_SPIRAL29, I_WY8_K9R2, I_SPIRAL49, I_WY8_K9R4,
+                I_WY16_K15R6, I_WY16_K9R2, I_WY16_K9R4 };
 
 static int find_instance(const CodecParams& c) {
     if (same_code<CodeK15R6>(c)) {
         if (c.policy == P_KA9Q_S16_615) return I_KA9Q615;
         if (c.policy == P_SPIRAL_615) return I_SPIRAL615;
         if (c.policy == P_WY_U8) return I_WY8_K15R6;
+        if (c.policy == P_WY_U16) return I_WY16_K15R6;
     } else if (same_code<CodeK9R2>(c)) {
         if (c.policy == P_KA9Q_U8_MOD) return I_KA9Q29;
         if (c.policy == P_SPIRAL_R2) return I_SPIRAL29;
         if (c.policy == P_WY_U8) return I_WY8_K9R2;
+        if (c.policy == P_WY_U16) return I_WY16_K9R2;
     } else if (same_code<CodeK9R4>(c)) {
         if (c.policy == P_SPIRAL_R4) return I_SPIRAL49;
         if (c.policy == P_WY_U8) return I_WY8_K9R4;
+        if (c.policy == P_WY_U16) return I_WY16_K9R4;
     }
     return I_NONE;
 }
@@ -605,6 +636,17 @@ bool grp_supported(const CodecParams& c) {
     if (c.policy == P_WY_U8 && (c.max_error > 255 || c.renorm_threshold > 255 || c.init_other > 255 ||
                                 c.init_start > 255 || c.max_error < 0 || c.init_other < 0 || c.init_start < 0))
         return false;
+    // wy-u16: the 16-bit lane window must hold rebase threshold + metric spread + two (capped) branch metrics
+    if (c.policy == P_WY_U16) {
+        if (c.max_error <= 0 || c.init_start < 0 || c.init_other < 0 || c.renorm_threshold < 0 ||
+            c.init_start > 65535 || c.init_other > 65535 || c.renorm_threshold > 65535) return false;
+        const long long cap = 2LL * c.max_error;
+        long long spread = (long long)(c.K - 1) * cap;
+        const long long init_spread = (long long)c.init_other - c.init_start;
+        if (init_spread > spread) spread = init_spread;
+        if (-init_spread > spread) spread = -init_spread;
+        if (4096 + spread + 2 * cap > 64000) return false;
+    }
     return true;
 }
 
@@ -628,6 +670,9 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
     case grp::I_WY8_K9R2: return grp::launch_one<P_WY_U8, grp::CodeK9R2>(a, st);
     case grp::I_SPIRAL49: return grp::launch_one<P_SPIRAL_R4, grp::CodeK9R4>(a, st);
     case grp::I_WY8_K9R4: return grp::launch_one<P_WY_U8, grp::CodeK9R4>(a, st);
+    case grp::I_WY16_K15R6: return grp::launch_one<P_WY_U16, grp::CodeK15R6>(a, st);
+    case grp::I_WY16_K9R2: return grp::launch_one<P_WY_U16, grp::CodeK9R2>(a, st);
+    case grp::I_WY16_K9R4: return grp::launch_one<P_WY_U16, grp::CodeK9R4>(a, st);
     default: return cudaErrorInvalidValue;
     }
 }

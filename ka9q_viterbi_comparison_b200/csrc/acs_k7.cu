@@ -39,6 +39,10 @@ struct Code {
 template <int POLICY>
 struct Arith {
     static constexpr bool modular = (POLICY == P_KA9Q_U8_MOD);
+    static constexpr bool wide = (POLICY == P_WY_U16);          // u16 metrics: offset may be negative, rebase by minimum
+    static constexpr int TOP = wide ? 65535 : 255;
+    static constexpr int SB = wide ? 2 : 1;                     // bytes per input symbol
+    __device__ __forceinline__ static int bm_cap(int C) { return wide ? 2 * C : 255; }
     // candidate = old + branch metric (saturating at the clamp for the u8-saturating policies)
     __device__ __forceinline__ static uint32_t add(uint32_t a, uint32_t w, uint32_t clamp) {
         if (modular) return a + w;                 // lanes never overflow (rebased every 64 periods)
@@ -57,6 +61,14 @@ __device__ __forceinline__ void bm_pair(const int* sym, int C, int soft_hi, int 
             const int bt = ((CW >> i) & 1) ? soft_hi : soft_lo;
             int e = clamp_i(bt - sym[i], -128, 127);
             tot = min(tot + abs(e), 255);
+        }
+        v = tot;
+    } else if (POLICY == P_WY_U16) {
+        int tot = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int bt = ((CW >> i) & 1) ? soft_hi : soft_lo;
+            tot = min(tot + abs(clamp_i(bt - sym[i], -32768, 32767)), 65535);
         }
         v = tot;
     } else if (POLICY == P_KA9Q_U8_MOD || POLICY == P_SPIRAL_R2) {
@@ -172,7 +184,9 @@ __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7
     constexpr int R = CODE::R, NCW = 1 << R;
     uint32_t bm[NCW], cm[NCW];
     BmFill<POLICY, CODE, 0, NCW>::run(sym, a.C, a.soft_hi, a.soft_lo, bm, cm);
-    const uint32_t clamp = (255u + off) * 0x10001u;
+    // registers hold true + off (off is a wrapping 32-bit integer, negative for the u16 policy); the clamp is exact
+    // whenever it can bind and otherwise sits above every reachable lane value
+    const uint32_t clamp = (uint32_t)min(Arith<POLICY>::TOP + (int)off, 65535 - Arith<POLICY>::bm_cap(a.C)) * 0x10001u;
     uint32_t acc0 = 0, acc1 = 0;
 
     if constexpr (P < NB - 1) {
@@ -195,14 +209,20 @@ __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7
         mn = __vminu2(mn, w[NW - 1]);
         const uint32_t m = min(mn & 0xffffu, mn >> 16);
         const int true0 = (int)(w[0] & 0xffffu) - (int)off;
-        const bool need = (POLICY == P_WY_U8) ? (true0 >= a.thr) : (true0 > a.thr);
+        const bool need = (POLICY == P_WY_U8 || POLICY == P_WY_U16) ? (true0 >= a.thr) : (true0 > a.thr);
         if (need) off = m;
+        if (Arith<POLICY>::wide && m > 4096u) {      // keep the u16 window at the bottom of the lanes
+            const uint32_t sub = m * 0x10001u;
+#pragma unroll
+            for (int i = 0; i < NW; i++) w[i] -= sub;
+            off -= m;
+        }
     }
 }
 
 // ---- symbol fetch: one period (6 steps * R bytes) per frame into registers ---------------------------
-template <int R> struct PeriodBuf {
-    static constexpr int BYTES = NB * R;
+template <int R, int SB> struct PeriodBuf {
+    static constexpr int BYTES = NB * R * SB;
     static constexpr int WORDS = (BYTES + 3) / 4;
     uint32_t w[WORDS];
     __device__ __forceinline__ void load(const unsigned char* p) {
@@ -224,15 +244,15 @@ template <int R> struct PeriodBuf {
     __device__ __forceinline__ void symbols(int step, int* sym) const {
 #pragma unroll
         for (int i = 0; i < R; i++) {
-            const int b = step * R + i;
-            const uint32_t v = (w[b >> 2] >> ((b & 3) * 8)) & 0xffu;
-            sym[i] = (POLICY == P_WY_U8) ? (int)(int8_t)v : (int)v;
+            const int b = (step * R + i) * SB;
+            const uint32_t v = (w[b >> 2] >> ((b & 3) * 8)) & (SB == 2 ? 0xffffu : 0xffu);
+            sym[i] = (SB == 2) ? (int)(int16_t)v : (POLICY == P_WY_U8) ? (int)(int8_t)v : (int)v;
         }
     }
 };
 
 template <int POLICY, class CODE, int P>
-__device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE::R>& buf, const K7Args& a,
+__device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE::R, Arith<POLICY>::SB>& buf, const K7Args& a,
                                          uint32_t& off, unsigned long long* dec_row) {
     int sym[CODE::R];
     buf.template symbols<POLICY>(P, sym);
@@ -268,16 +288,28 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
         }
     }
 
+    if (Arith<POLICY>::wide) {     // u16 metrics may start anywhere in [0, 65535]: bring the window down first
+        uint32_t mn = w[0];
+#pragma unroll
+        for (int i = 1; i < NW; i++) mn = __vminu2(mn, w[i]);
+        const uint32_t m = min(mn & 0xffffu, mn >> 16);
+#pragma unroll
+        for (int i = 0; i < NW; i++) w[i] -= m * 0x10001u;
+        off = 0u - m;
+    }
+
     const unsigned char* sp = a.syms + (size_t)f * a.sym_stride;
     unsigned long long* drow = a.dec + (size_t)a.step0 * a.n_frames + f;
     const size_t dstride = (size_t)a.n_frames;
 
     const int periods = a.nsteps / NB;
-    PeriodBuf<R> cur, nxt;
+    constexpr int SB = Arith<POLICY>::SB;
+    using PBuf = PeriodBuf<R, SB>;
+    PBuf cur, nxt;
     if (periods > 0) cur.load(sp);
 #pragma unroll 1
     for (int pd = 0; pd < periods; pd++) {
-        if (pd + 1 < periods) nxt.load(sp + (size_t)(pd + 1) * NB * R);
+        if (pd + 1 < periods) nxt.load(sp + (size_t)(pd + 1) * NB * R * SB);
         unsigned long long d0, d1, d2, d3, d4, d5;
         run_step<POLICY, CODE, 0>(w, cur, a, off, &d0);
         run_step<POLICY, CODE, 1>(w, cur, a, off, &d1);
@@ -300,7 +332,7 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
                 const uint32_t sub = (m & ~255u) >= 256u ? (m & ~255u) - 256u : 0u;
 #pragma unroll
                 for (int i = 0; i < NW; i++) w[i] -= sub * 0x10001u;
-            } else {
+            } else if (!Arith<POLICY>::wide) {
 #pragma unroll
                 for (int i = 0; i < NW; i++) w[i] -= off * 0x10001u;    // every lane >= off: no borrow
                 off = 0;
@@ -311,14 +343,14 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     // ---- tail: fewer than 6 steps left ----
     const int rem = a.nsteps - periods * NB;
     if (rem > 0) {
-        PeriodBuf<R> tb;
-        const unsigned char* tp = sp + (size_t)periods * NB * R;
+        PBuf tb;
+        const unsigned char* tp = sp + (size_t)periods * NB * R * SB;
 #pragma unroll
-        for (int i = 0; i < PeriodBuf<R>::WORDS; i++) {
+        for (int i = 0; i < PBuf::WORDS; i++) {
             uint32_t v = 0;
 #pragma unroll
             for (int b = 0; b < 4; b++)
-                if (i * 4 + b < rem * R) v |= (uint32_t)__ldg(tp + i * 4 + b) << (8 * b);
+                if (i * 4 + b < rem * R * SB) v |= (uint32_t)__ldg(tp + i * 4 + b) << (8 * b);
             tb.w[i] = v;
         }
         unsigned long long d;
@@ -361,12 +393,15 @@ static int find_instance(const CodecParams& c) {
         if (c.policy == P_KA9Q_U8_MOD) return 0;
         if (c.policy == P_SPIRAL_R2) return 1;
         if (c.policy == P_WY_U8) return 2;
+        if (c.policy == P_WY_U16) return 6;
     }
     if (c.R == 4 && c.poly[0] == 121 && c.poly[1] == 117 && c.poly[2] == 91 && c.poly[3] == 111) {
         if (c.policy == P_SPIRAL_R4) return 3;
         if (c.policy == P_WY_U8) return 4;
+        if (c.policy == P_WY_U16) return 7;
     }
     if (c.R == 3 && c.poly[0] == 91 && c.poly[1] == 117 && c.poly[2] == 121 && c.policy == P_WY_U8) return 5;
+    if (c.R == 3 && c.poly[0] == 91 && c.poly[1] == 117 && c.poly[2] == 121 && c.policy == P_WY_U16) return 8;
     return -1;
 }
 
@@ -376,6 +411,16 @@ bool k7_supported(const CodecParams& c) {
     if (k7::find_instance(c) < 0) return false;
     // wy-u8: the offset representation needs headroom above the saturation point
     if (c.policy == P_WY_U8 && (c.max_error > 255 || c.renorm_threshold > 255 || c.init_other > 255)) return false;
+    if (c.policy == P_WY_U16) {     // the lane window: rebase threshold + metric spread + two capped branch metrics
+        if (c.max_error <= 0 || c.init_start < 0 || c.init_other < 0 || c.renorm_threshold < 0 ||
+            c.init_start > 65535 || c.init_other > 65535 || c.renorm_threshold > 65535) return false;
+        const long long cap = 2LL * c.max_error;
+        long long spread = (long long)(c.K - 1) * cap;
+        const long long init_spread = (long long)c.init_other - c.init_start;
+        if (init_spread > spread) spread = init_spread;
+        if (-init_spread > spread) spread = -init_spread;
+        if (4096 + spread + 2 * cap > 32000) return false;   // the arithmetic decision needs |lo - hi| < 2^15
+    }
     return true;
 }
 
@@ -396,6 +441,9 @@ cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_str
     case 3: return k7::launch_one<P_SPIRAL_R4, k7::CodeK7R4>(a, st);
     case 4: return k7::launch_one<P_WY_U8, k7::CodeK7R4>(a, st);
     case 5: return k7::launch_one<P_WY_U8, k7::CodeK7R3>(a, st);
+    case 6: return k7::launch_one<P_WY_U16, k7::CodeK7R2>(a, st);
+    case 7: return k7::launch_one<P_WY_U16, k7::CodeK7R4>(a, st);
+    case 8: return k7::launch_one<P_WY_U16, k7::CodeK7R3>(a, st);
     default: return cudaErrorInvalidValue;
     }
 }

@@ -153,6 +153,8 @@ struct b200v_batch {
     uint8_t* d_cw = nullptr;
     uint8_t* d_row_phase = nullptr;   // K=7 register family: phase of the step that wrote each decision row
     int* d_results = nullptr;
+    int* d_scan = nullptr;       // wy-u16 symbol range check
+    bool user_variant = false;   // set_variant() was called: no automatic family changes
     // lazily allocated staging for the host-pointer entry points
     void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
     uint8_t* d_out_stage = nullptr; size_t out_stage_bytes = 0;
@@ -162,7 +164,7 @@ static void free_all(b200v_batch* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
-    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase);
+    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase); cudaFree(h->d_scan);
     cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
@@ -263,6 +265,7 @@ extern "C" int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream) {
 
 extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    h->user_variant = variant != 0;
     if (variant == 0) variant = h->has_fast ? 2 : 1;
     if (variant != h->variant && h->cursor != 0)
         return fail(B200V_ERR_STATE, "the kernel family can only change right after init (decision layouts differ)");
@@ -279,7 +282,51 @@ extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     h->launches++;
     h->cursor = 0;
     h->cur_metrics = 0;
+    if (!h->user_variant && h->layout != DL_CANONICAL) {     // back to the automatic family (wy-u16 may have left it)
+        h->variant = h->has_fast ? 2 : 1;
+        h->layout = h->has_fast ? h->fast_layout : DL_BALLOT_FRAME_MAJOR;
+    }
     return B200V_OK;
+}
+
+// ---- wy-u16: symbol range check ---------------------------------------------------------------------------
+// The specialised u16 kernels size their 16-bit lane window for branch metrics up to 2 * soft_decision_max_error
+// (true for every symbol within about three times the soft-decision range). int16 symbols outside that range are
+// legal input for the reference, so every update of a wy-u16 instance first reduces max |symbol| on the device;
+// a batch that exceeds the range is decoded by the generic kernel (exact for any input) instead.
+__global__ void max_abs_s16_kernel(const int16_t* syms, size_t stride_elems, int per_frame, int n_frames, int* out) {
+    int m = 0;
+    const size_t total = (size_t)per_frame * n_frames;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t f = i / per_frame, k = i - f * per_frame;
+        const int v = (int)syms[f * stride_elems + k];
+        m = max(m, v < 0 ? -v : v);
+    }
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
+static int wy16_symbol_limit(const CodecParams& c) {
+    const int bt = c.soft_hi > -c.soft_lo ? (c.soft_hi > 0 ? c.soft_hi : -c.soft_hi) : (c.soft_lo < 0 ? -c.soft_lo : c.soft_lo);
+    return 2 * c.max_error / c.R - bt;      // R * (|bt| + |s|) <= 2 * max_error
+}
+
+// Returns 1 if every symbol of this update is inside the specialised kernels' range, 0 if not, < 0 on error.
+static int wy16_symbols_in_range(b200v_batch* h, const void* d_syms, size_t stride_bytes, int nsteps) {
+    if (!h->d_scan) CUDA_TRY(cudaMalloc(&h->d_scan, sizeof(int)));
+    CUDA_TRY(cudaMemsetAsync(h->d_scan, 0, sizeof(int), h->stream));
+    const int per_frame = nsteps * h->c.R;
+    const size_t total = (size_t)per_frame * h->n_frames;
+    int blocks = (int)((total + 1023) / 1024);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    max_abs_s16_kernel<<<blocks, 256, 0, h->stream>>>((const int16_t*)d_syms, stride_bytes / 2, per_frame, h->n_frames, h->d_scan);
+    CUDA_TRY(cudaGetLastError());
+    h->launches++;
+    int m = 0;
+    CUDA_TRY(cudaMemcpyAsync(&m, h->d_scan, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return m <= wy16_symbol_limit(h->c) ? 1 : 0;
 }
 
 // Launch the ACS kernel of the instance's family for frames [f0, f0 + cnt) on stream st.
@@ -325,6 +372,17 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
     if (nsteps > 0 && frame_stride_bytes < (size_t)nsteps * c.R * c.sym_bytes && h->n_frames > 1)
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
+    if (c.policy == P_WY_U16 && h->variant == 2 && nsteps > 0) {
+        const int ok = wy16_symbols_in_range(h, d_syms, frame_stride_bytes, nsteps);
+        if (ok < 0) return ok;
+        if (!ok) {
+            if (h->cursor != 0)
+                return fail(B200V_ERR_ARG, "int16 symbols beyond +-%d in a continued update: the specialised u16 kernels "
+                            "cannot take over mid-frame; select the generic family (variant 1) after init",
+                            wy16_symbol_limit(c));
+            h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR;      // exact for any input
+        }
+    }
     CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
     int rc = launch_update_range(h, d_syms, frame_stride_bytes, nsteps, h->cursor, 0, h->n_frames, h->stream);
     if (rc) return rc;
@@ -428,7 +486,7 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
     const size_t srow = (size_t)h->frame_steps * c.R * c.sym_bytes;
     const size_t orow = (nbits + 7) / 8;
     const int min_chunk = 2048;
-    if (h->layout == DL_CANONICAL || h->n_frames < 2 * min_chunk || orow == 0) {
+    if (h->layout == DL_CANONICAL || c.policy == P_WY_U16 || h->n_frames < 2 * min_chunk || orow == 0) {
         int rc = b200v_batch_init(h, 0);
         if (rc) return rc;
         rc = b200v_batch_update(h, syms, srow, h->frame_steps);

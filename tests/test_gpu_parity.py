@@ -292,7 +292,8 @@ def test_full_size_round_trip_properties():
 
 
 @pytest.mark.parametrize("name", ["ka9q615", "spiral615", "wy_sse_u8_k15r6", "spiral29", "spiral49", "wy_sse_u8_k9r2",
-                                  "wy_sse_u8_k9r4", "ka9q29"])
+                                  "wy_sse_u8_k9r4", "ka9q29", "wy_sse_u16_k15r6", "wy_sse_u16_k9r2", "wy_sse_u16_k9r4",
+                                  "wy_sse_u16_k7r2", "wy_sse_u16_k7r4", "spiral47", "wy_sse_u8_k7r3"])
 def test_long_frames_all_families(name):
     """BASELINE-length frames (2048 bits): many renormalisations, lane rebasing of the group kernels, the
     partial last group (T mod 5 != 0) and streaming across kernel launches at odd phases."""
@@ -408,3 +409,32 @@ def test_pipelined_batch_decode_matches_whole_batch_launch(name):
             assert np.array_equal(out_pipe[f], qo), f
             assert np.array_equal(d, qd), f
             q.close()
+
+
+@pytest.mark.parametrize("name", ["wy_sse_u16_k7r2", "wy_sse_u16_k9r4", "wy_sse_u16_k15r6"])
+def test_wy_u16_out_of_range_symbols_take_the_generic_family(name):
+    """int16 symbols far outside the soft-decision range are legal input for the reference (saturating |bt - s|);
+    the specialised u16 kernels size their lane window for in-range symbols, so the library checks every update
+    and decodes such a batch with the generic kernel. Both cases must match the oracle bit for bit."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    T = 90 if K == 15 else 300
+    nbits = T - (K - 1)
+    rng = np.random.default_rng(16)
+    in_range = rng.integers(-127, 128, size=(3, T * R)).astype(np.int16)
+    wild = rng.integers(-32768, 32768, size=(3, T * R)).astype(np.int16)
+    wild[1, ::7] = -32768
+    wild[2, ::5] = 32767
+    with kv.BatchDecoder(codec, T, 3, K=K, R=R) as dec:
+        for syms, expect_variant in ((in_range, 2), (wild, 1), (in_range, 2)):
+            dec.reset()
+            dec.update(syms)
+            assert dec.variant == expect_variant
+            out = dec.chainback(nbits)
+            for f in range(3):
+                q = o.Oracle(c, T)
+                qo, qd = q.decode(syms[f], nbits)
+                assert np.array_equal(dec.decisions(f, 0, T), qd), (expect_variant, f)
+                assert np.array_equal(dec.metrics(f), q.metrics()), (expect_variant, f)
+                assert np.array_equal(out[f], qo), (expect_variant, f)
+                q.close()
