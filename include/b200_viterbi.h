@@ -167,6 +167,18 @@ int b200v_batch_generate_dev(b200v_batch* h, void* d_syms, size_t sym_frame_stri
                              unsigned nbits, uint64_t seed, uint64_t frame0,
                              int amp_q8, int sigma_q8, int mean_q8, int lo, int hi);
 
+/* ---- depuncturing front-end ----
+ * The symbol loop of decode_punctured_symbols (williamyang_viterbi_lib/examples/helpers/puncture_code_helpers.h:17-55)
+ * for all frames: output symbol k (k < n_out_syms) = the next transmitted symbol if puncture_code[k % code_len] is
+ * non-zero, else unpunctured_value; the code index starts at 0 on every call, so a frame made of segments with
+ * different codes (run_punctured_decoder.cpp:260-282) is one call per segment, advancing in_offset_syms by *consumed
+ * and out_offset_syms by n_out_syms. Frame f reads d_punctured + f*in_stride_bytes and writes d_syms +
+ * f*out_stride_bytes (symbols of the instance's codec: u8, int8 or int16). puncture_code is a host array of
+ * code_len <= 256 flags. *consumed (may be NULL) = transmitted symbols used per frame. Asynchronous on the stream. */
+int b200v_batch_depuncture_dev(b200v_batch* h, const void* d_punctured, size_t in_stride_bytes, size_t in_offset_syms,
+                               const uint8_t* puncture_code, int code_len, void* d_syms, size_t out_stride_bytes,
+                               size_t out_offset_syms, int n_out_syms, int unpunctured_value, int* consumed);
+
 /* ---- multi-GPU inside one process (frames are independent; no collective) ----
  * Shard g of G owns the contiguous frames [g*B/G, (g+1)*B/G). */
 int b200v_shard_range(int n_frames, int n_shards, int shard, int* frame0, int* count);

@@ -685,6 +685,30 @@ extern "C" int b200v_batch_generate_dev(b200v_batch* h, void* d_syms, size_t sym
 }
 
 // ---------------------------------------------------------------------------------------------------
+// depuncturing front-end
+// ---------------------------------------------------------------------------------------------------
+extern "C" int b200v_batch_depuncture_dev(b200v_batch* h, const void* d_punctured, size_t in_stride_bytes,
+                                          size_t in_offset_syms, const uint8_t* puncture_code, int code_len,
+                                          void* d_syms, size_t out_stride_bytes, size_t out_offset_syms,
+                                          int n_out_syms, int unpunctured_value, int* consumed) {
+    if (!h || !d_punctured || !d_syms || !puncture_code) return fail(B200V_ERR_ARG, "NULL argument");
+    if (code_len <= 0 || code_len > MAX_PUNCTURE_LEN)
+        return fail(B200V_ERR_ARG, "puncture code length %d out of range [1,%d]", code_len, MAX_PUNCTURE_LEN);
+    if (n_out_syms < 0) return fail(B200V_ERR_ARG, "negative symbol count");
+    DepunctureArgs a{};
+    a.in = d_punctured; a.in_stride = in_stride_bytes; a.in_offset = in_offset_syms;
+    a.out = d_syms; a.out_stride = out_stride_bytes; a.out_offset = out_offset_syms;
+    a.n_out = n_out_syms; a.code_len = code_len; a.fill = unpunctured_value;
+    a.prefix[0] = 0;
+    for (int j = 0; j < code_len; j++) a.prefix[j + 1] = (uint16_t)(a.prefix[j] + (puncture_code[j] ? 1 : 0));
+    if (consumed) *consumed = (n_out_syms / code_len) * a.prefix[code_len] + a.prefix[n_out_syms % code_len];
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(launch_depuncture(a, h->c.sym_bytes, h->n_frames, h->stream));
+    h->launches++;
+    return B200V_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // memory helpers
 // ---------------------------------------------------------------------------------------------------
 extern "C" void* b200v_device_alloc(int device, size_t bytes) {

@@ -1,0 +1,38 @@
+// depuncture.cu -- depuncturing front-end: expands a punctured symbol stream to the full-rate stream
+// the ACS kernels consume. Takes the role of the symbol loop of decode_punctured_symbols
+// (williamyang_viterbi_lib/examples/helpers/puncture_code_helpers.h:17-55): output symbol k takes the next
+// transmitted symbol where puncture_code[k mod L] is set and `unpunctured_symbol_value` elsewhere; the code index
+// starts at 0 for every call (the reference calls it once per segment of a frame, run_punctured_decoder.cpp:260-282).
+// One thread per output symbol: rank(k) = (k / L) * ones + prefix[k mod L] transmitted symbols precede position k.
+// Pure data movement: HBM-bound (reads `ones/L` of what it writes).
+#include "kernels.h"
+
+namespace b200v {
+
+namespace {
+
+template <typename T>
+__global__ void depuncture_kernel(const DepunctureArgs a) {
+    const int frame = blockIdx.y;
+    const T* in = reinterpret_cast<const T*>((const unsigned char*)a.in + (size_t)frame * a.in_stride) + a.in_offset;
+    T* out = reinterpret_cast<T*>((unsigned char*)a.out + (size_t)frame * a.out_stride) + a.out_offset;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < a.n_out; k += gridDim.x * blockDim.x) {
+        const int q = k / a.code_len, j = k - q * a.code_len;
+        const bool kept = a.prefix[j + 1] != a.prefix[j];
+        out[k] = kept ? in[(size_t)q * a.prefix[a.code_len] + a.prefix[j]] : (T)a.fill;
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_depuncture(const DepunctureArgs& a, int sym_bytes, int n_frames, cudaStream_t st) {
+    if (n_frames <= 0 || a.n_out <= 0) return cudaSuccess;
+    int bx = (a.n_out + 255) / 256;
+    if (bx > 64) bx = 64;
+    const dim3 grid((unsigned)bx, (unsigned)n_frames);
+    if (sym_bytes == 2) depuncture_kernel<int16_t><<<grid, 256, 0, st>>>(a);
+    else depuncture_kernel<uint8_t><<<grid, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace b200v

@@ -64,6 +64,18 @@ struct ChainbackArgs {
 };
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st);
 
+// ---- depuncturing front-end (depuncture.cu) -------------------------------------------------------------
+constexpr int MAX_PUNCTURE_LEN = 256;
+struct DepunctureArgs {
+    const void* in; size_t in_stride; size_t in_offset;     // transmitted symbols; stride in bytes, offset in symbols
+    void* out; size_t out_stride; size_t out_offset;        // full-rate symbols
+    int n_out;                                              // output symbols to produce per frame
+    int code_len;
+    int fill;                                               // value of a symbol that was not transmitted
+    uint16_t prefix[MAX_PUNCTURE_LEN + 1];                  // prefix[j] = kept positions among code[0..j)
+};
+cudaError_t launch_depuncture(const DepunctureArgs& a, int sym_bytes, int n_frames, cudaStream_t st);
+
 // ---- synthetic input generator (generate.cu) ------------------------------------------------------
 struct GenerateArgs {
     CodecParams c;

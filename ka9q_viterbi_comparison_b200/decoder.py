@@ -91,6 +91,7 @@ def load_library():
         "b200v_batch_last_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "b200v_batch_launch_count": (C.c_longlong, [vp]),
         "b200v_batch_generate_dev": (i32, [vp, vp, sz, vp, sz, u32, u64, u64, i32, i32, i32, i32, i32]),
+        "b200v_batch_depuncture_dev": (i32, [vp, vp, sz, sz, vp, i32, vp, sz, sz, i32, i32, C.POINTER(i32)]),
         "b200v_shard_range": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
         "b200v_sharded_create": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(WyConfig)]),
         "b200v_sharded_destroy": (None, [vp]),
@@ -120,7 +121,7 @@ EXPORTED_SYMBOLS = [
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
     "b200v_batch_chainback_results", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_batch_sync", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
-    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_shard_range", "b200v_sharded_create",
+    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_shard_range", "b200v_sharded_create",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
     "b200v_sharded_last_error", "b200v_device_alloc", "b200v_device_free",
     "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
@@ -217,6 +218,15 @@ class BatchDecoder:
     def decode_dev(self, d_syms, sym_stride, d_out, out_stride, nbits):
         """init + update + chainback with device buffers (b200v_batch_decode_dev); asynchronous."""
         _check(self.lib.b200v_batch_decode_dev(self.h, _ptr(d_syms), sym_stride, _ptr(d_out), out_stride, nbits))
+
+    def depuncture_dev(self, d_punctured, in_stride, in_offset, code, d_syms, out_stride, out_offset, n_out, fill=0):
+        """One segment of decode_punctured_symbols' symbol expansion for all frames; returns symbols consumed."""
+        code = np.ascontiguousarray(code, dtype=np.uint8)
+        used = C.c_int(0)
+        _check(self.lib.b200v_batch_depuncture_dev(self.h, _ptr(d_punctured), in_stride, in_offset, code.ctypes.data,
+                                                   len(code), _ptr(d_syms), out_stride, out_offset, n_out, fill,
+                                                   C.byref(used)))
+        return used.value
 
     def generate_dev(self, d_syms, sym_stride, d_data, data_stride, nbits, seed, frame0, amp_q8, sigma_q8,
                      mean_q8, lo, hi):

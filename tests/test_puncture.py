@@ -1,0 +1,115 @@
+"""Depuncturing front-end. CPU: the restatement in oracle/puncture_oracle.py equals the reference's
+own helpers (compiled into oracle/_ref). GPU: b200v_batch_depuncture_dev equals the restatement; a DAB fast
+information channel frame (K=7 r=1/4, codes PI_16 / PI_15 / PI_X) punctured on the host decodes to the data, and
+matches the oracle decoder fed with the restated depunctured stream."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import _oracle as o
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+import puncture_oracle as po  # noqa: E402
+
+
+def _ref():
+    if not o.ref_available():
+        pytest.skip("oracle/_ref not built")
+    lib = o.ref_lib()
+    if not hasattr(lib, "kvref_depuncture_s8"):
+        pytest.skip("oracle/_ref predates the puncture shim")
+    lib.kvref_depuncture_s8.restype = C.c_long
+    lib.kvref_depuncture_s16.restype = C.c_long
+    lib.kvref_puncture_encode_s8.restype = C.c_long
+    return lib
+
+
+@pytest.mark.parametrize("R", [2, 4])
+def test_depuncture_restatement_matches_reference_helper(R):
+    lib = _ref()
+    rng = np.random.default_rng(7)
+    for code in (po.PI_16, po.PI_15, po.PI_X, np.array([1, 0, 1, 1, 0, 1, 1], dtype=np.uint8)):
+        for requested in (R, 24, 32 * R * 3, 100 * R):
+            n_in = int(code.sum()) * (requested // len(code) + 2)
+            for dt, fn in ((np.int8, lib.kvref_depuncture_s8), (np.int16, lib.kvref_depuncture_s16)):
+                tx = rng.integers(-100, 100, n_in).astype(dt)
+                out = np.zeros(requested + R, dtype=dt)
+                used = fn(C.c_int(R), C.c_void_p(tx.ctypes.data), C.c_size_t(n_in), C.c_void_p(code.ctypes.data),
+                          C.c_size_t(len(code)), C.c_size_t(requested), C.c_int(5), C.c_void_p(out.ctypes.data))
+                want, want_used = po.depuncture(tx, code, requested, 5, R)
+                assert used == want_used
+                assert np.array_equal(out[:len(want)], want)
+
+
+def test_puncture_restatement_matches_reference_encoder():
+    lib = _ref()
+    c = o.codec_by_name("wy_sse_u8_k7r4")
+    poly = (C.c_int * 4)(*[c.poly[i] for i in range(4)])
+    data = o.random_bytes(3, 0, 12)
+    out = np.zeros(12 * 8 * 4 + 64, dtype=np.int8)
+    n = lib.kvref_puncture_encode_s8(C.c_int(7), C.c_int(4), poly, C.c_void_p(data.ctypes.data), C.c_size_t(12),
+                                     C.c_void_p(po.PI_15.ctypes.data), C.c_size_t(32), C.c_int(1),
+                                     C.c_void_p(po.PI_X.ctypes.data), C.c_size_t(24), C.c_int(3), C.c_int(-3),
+                                     C.c_void_p(out.ctypes.data), C.c_size_t(out.size))
+    _, full = o.make_frame(c, 12, 0.0, seed=3, frame=0)          # noiseless full-rate symbols incl. the tail
+    want = np.concatenate([po.puncture(full[:12 * 8 * 4], po.PI_15), po.puncture(full[12 * 8 * 4:], po.PI_X)])
+    assert n == want.size
+    assert np.array_equal(out[:n], want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["wy_sse_u8_k7r4", "wy_sse_u16_k7r4", "spiral47"])
+def test_gpu_depuncture_and_dab_fic_round_trip(name):
+    import torch
+    import ka9q_viterbi_comparison_b200 as kv
+    from test_gpu_parity import CASES
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes, n_frames = 96, 5                                   # 768 bits = 21 + 3 blocks of 32 bits
+    nbits = nbytes * 8
+    T = nbits + K - 1
+    lo, hi = o.soft_range(c)
+    fill = (lo + hi + 1) // 2                                  # erasure: 0 for the wy alphabets, 128 for 0..255
+    dt = o.sym_dtype(c)
+    segs = po.dab_fic_segments(R)
+    datas, txs, fulls = [], [], []
+    for f in range(n_frames):
+        d, full = o.make_frame(c, nbytes, 0.4 if f else 0.0, seed=21, frame=f)
+        pos, parts = 0, []
+        for code, n_out in segs:
+            parts.append(po.puncture(full[pos:pos + n_out], code))
+            pos += n_out
+        assert pos == T * R
+        datas.append(d); txs.append(np.concatenate(parts)); fulls.append(full)
+    n_tx = txs[0].size
+    tx = np.stack(txs).astype(dt)
+    sb = np.dtype(dt).itemsize
+    d_tx = torch.from_numpy(tx.view(np.uint8).reshape(n_frames, -1).copy()).cuda()
+    d_syms = torch.zeros(n_frames * T * R * sb, dtype=torch.uint8, device="cuda")
+    d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        ip = op = 0
+        for code, n_out in segs:
+            ip += dec.depuncture_dev(d_tx, n_tx * sb, ip, code, d_syms, T * R * sb, op, n_out, fill)
+            op += n_out
+        assert ip == n_tx and op == T * R
+        dec.sync()
+        got = d_syms.cpu().numpy().view(dt).reshape(n_frames, T * R)
+        dec.decode_dev(d_syms, T * R * sb, d_out, nbytes, nbits)
+        dec.sync()
+        out = d_out.cpu().numpy().reshape(n_frames, nbytes)
+    for f in range(n_frames):
+        ip, parts = 0, []
+        for code, n_out in segs:
+            s, used = po.depuncture(tx[f, ip:], code, n_out, fill, R)
+            parts.append(s); ip += used
+        want = np.concatenate(parts)
+        assert np.array_equal(got[f], want), f
+        q = o.Oracle(c, T)
+        qo, _ = q.decode(want, nbits)
+        assert np.array_equal(out[f], qo), f
+        q.close()
+    assert np.array_equal(out[0], datas[0])                    # the noiseless frame decodes to the data
