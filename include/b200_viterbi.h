@@ -123,6 +123,14 @@ int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t frame_stri
                               unsigned endstate);
 int b200v_batch_chainback(b200v_batch* h, uint8_t* data, size_t frame_stride_bytes, unsigned nbits,
                           unsigned endstate);
+/* Traceback of an unterminated stream (the reference's resumable update + get_error(),
+ * viterbi_decoder_core.h:193-197, give the pieces): every frame is traced back from its own best state -- the
+ * smallest path metric after the steps consumed so far, ties to the lowest state -- through all rows written
+ * since init: nbits must equal steps_done - (K-1). d_best_states (device, n_frames unsigned, may be NULL) receives
+ * the states used. Decoded bit n is the input bit of trellis step n (the last K-1 input bits are the best state
+ * itself); a sliding-window caller keeps all but the last `depth` bits. Asynchronous on the stream. */
+int b200v_batch_chainback_best_dev(b200v_batch* h, uint8_t* d_data, size_t frame_stride_bytes, unsigned nbits,
+                                   unsigned* d_best_states);
 /* Per-frame return value of the reference's chainback: the end-state path metric for KA9Q615
  * (viterbi615_sse2.cpp:76,90), 0 otherwise. Valid after a chainback; copies n_frames ints to the host. */
 int b200v_batch_chainback_results(b200v_batch* h, int* results);

@@ -153,6 +153,7 @@ struct b200v_batch {
     uint8_t* d_cw = nullptr;
     uint8_t* d_row_phase = nullptr;   // K=7 register family: phase of the step that wrote each decision row
     int* d_results = nullptr;
+    unsigned* d_best = nullptr;  // per-frame best end states (b200v_batch_chainback_best_dev)
     int* d_scan = nullptr;       // wy-u16 symbol range check
     bool user_variant = false;   // set_variant() was called: no automatic family changes
     // lazily allocated staging for the host-pointer entry points
@@ -164,7 +165,7 @@ static void free_all(b200v_batch* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
-    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase); cudaFree(h->d_scan);
+    cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase); cudaFree(h->d_scan); cudaFree(h->d_best);
     cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
@@ -419,13 +420,13 @@ extern "C" int b200v_batch_update(b200v_batch* h, const void* syms, size_t frame
 }
 
 static int launch_chainback_range(b200v_batch* h, uint8_t* d_data, size_t stride, unsigned nbits, unsigned endstate,
-                                  int f0, int cnt, cudaStream_t st) {
+                                  int f0, int cnt, cudaStream_t st, const unsigned* endstates = nullptr) {
     ChainbackArgs a{};
     a.c = h->c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
     a.row_phase = h->d_row_phase;
     a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
     a.metrics = h->cur_metrics ? h->d_metrics2 : h->d_metrics; a.out = d_data; a.out_stride = stride;
-    a.nbits = nbits; a.endstate = endstate; a.results = h->d_results;
+    a.nbits = nbits; a.endstate = endstate; a.endstates = endstates; a.results = h->d_results;
     CUDA_TRY(launch_chainback(a, st));
     h->launches++;
     return B200V_OK;
@@ -447,6 +448,28 @@ extern "C" int b200v_batch_chainback_dev(b200v_batch* h, uint8_t* d_data, size_t
     CUDA_TRY(cudaEventRecord(h->ev_c1, h->stream));
     h->timed_chainback = true;
     return B200V_OK;
+}
+
+// Traceback of an UNTERMINATED stream: every frame is traced from its own best state (smallest path
+// metric after the steps consumed so far) instead of a common end state; the caller of a sliding-window decoder
+// keeps the first nbits - depth bits and re-decodes the rest when more symbols have arrived.
+extern "C" int b200v_batch_chainback_best_dev(b200v_batch* h, uint8_t* d_data, size_t frame_stride_bytes, unsigned nbits,
+                                              unsigned* d_best_states) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (!d_data && nbits) return fail(B200V_ERR_ARG, "NULL output buffer");
+    const CodecParams& c = h->c;
+    const unsigned rows_needed = nbits + (c.policy == P_KA9Q_S16_224 ? 0u : (unsigned)(c.K - 1));
+    if (rows_needed != (unsigned)h->cursor)      // the best state belongs to the last row written
+        return fail(B200V_ERR_STATE, "best-state traceback covers all %d rows written since init: nbits must be %d, got %u",
+                    h->cursor, h->cursor - (int)(rows_needed - nbits), nbits);
+    CUDA_TRY(cudaSetDevice(h->device));
+    if (!h->d_best) CUDA_TRY(cudaMalloc(&h->d_best, (size_t)h->n_frames * sizeof(unsigned)));
+    CUDA_TRY(launch_best_state(c, h->cur_metrics ? h->d_metrics2 : h->d_metrics, h->d_best, h->n_frames, h->stream));
+    h->launches++;
+    if (d_best_states)
+        CUDA_TRY(cudaMemcpyAsync(d_best_states, h->d_best, (size_t)h->n_frames * sizeof(unsigned), cudaMemcpyDeviceToDevice,
+                                 h->stream));
+    return launch_chainback_range(h, d_data, frame_stride_bytes, nbits, 0, 0, h->n_frames, h->stream, h->d_best);
 }
 
 extern "C" int b200v_batch_chainback(b200v_batch* h, uint8_t* data, size_t frame_stride_bytes, unsigned nbits,

@@ -22,7 +22,7 @@ __global__ void chainback_kernel(const ChainbackArgs a) {
 
     if (a.c.policy == P_KA9Q_S16_224) {
         // no look-past-tail; emits (state & 1) into a byte that shifts right; stored when n % 8 == 0
-        unsigned state = a.endstate & ((1u << (K - 1)) - 1u);
+        unsigned state = (a.endstates ? a.endstates[f] : a.endstate) & ((1u << (K - 1)) - 1u);
         unsigned dbyte = 0;
         for (unsigned n = a.nbits; n-- > 0;) {
             dbyte = ((state & 1u) << 7) | (dbyte >> 1);
@@ -36,7 +36,7 @@ __global__ void chainback_kernel(const ChainbackArgs a) {
 
     const int add = (K - 1 < 8) ? 8 - (K - 1) : 0;
     const int sub = (K - 1 > 8) ? (K - 1) - 8 : 0;
-    unsigned reg = a.endstate % (unsigned)a.c.S;
+    unsigned reg = (a.endstates ? a.endstates[f] : a.endstate) % (unsigned)a.c.S;
     if (a.results) {
         int r = 0;
         if (a.c.policy == P_KA9Q_S16_615) r = (int)(int16_t)a.metrics[(size_t)f * a.c.S + reg];
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a
     const DecisionReader<DL_K7_INTERLEAVED> rd(a, f, tab);
     uint8_t* out = a.out + (size_t)f * a.out_stride;
     // K-1 = 6 < 8: the register keeps the state in its top 6 bits of a byte (ADDSHIFT = 2)
-    unsigned reg = (a.endstate % 64u) << 2;
+    unsigned reg = ((a.endstates ? a.endstates[f] : a.endstate) % 64u) << 2;
     if (a.results) a.results[f] = 0;
     unsigned n = a.nbits;
     while (n > 0) {
@@ -88,7 +88,42 @@ __global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a
     }
 }
 
+// smallest path metric of every frame: one block per frame, packed (key << 32 | state) minimum
+__global__ void best_state_kernel(const CodecParams c, const uint16_t* metrics, unsigned* best) {
+    const int f = blockIdx.x;
+    const uint16_t* m = metrics + (size_t)f * c.S;
+    const int m0 = (int)m[0];
+    unsigned long long b = ~0ull;
+    for (int i = threadIdx.x; i < c.S; i += blockDim.x) {
+        unsigned key;
+        if (c.policy == P_KA9Q_U8_MOD) key = (unsigned)((int)(int8_t)(m[i] - m0) + 128);
+        else if (c.policy == P_KA9Q_S16_615 || c.policy == P_KA9Q_S16_224) key = (unsigned)((int)(int16_t)m[i] + 32768);
+        else key = m[i];
+        const unsigned long long v = ((unsigned long long)key << 32) | (unsigned)i;
+        b = v < b ? v : b;
+    }
+    __shared__ unsigned long long s[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long t = __shfl_xor_sync(0xffffffffu, b, o);
+        b = t < b ? t : b;
+    }
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = b;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); w++) b = s[w] < b ? s[w] : b;
+        best[f] = (unsigned)b;
+    }
+}
+
 }  // namespace
+
+cudaError_t launch_best_state(const CodecParams& c, const uint16_t* metrics, unsigned* best, int n_frames, cudaStream_t st) {
+    if (n_frames <= 0) return cudaSuccess;
+    const int threads = c.S >= 256 ? 256 : (c.S < 32 ? 32 : c.S);
+    best_state_kernel<<<n_frames, threads, 0, st>>>(c, metrics, best);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
     if (a.count <= 0) return cudaSuccess;

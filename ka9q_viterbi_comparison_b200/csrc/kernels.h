@@ -60,9 +60,13 @@ struct ChainbackArgs {
     uint8_t* out;               // device; frame f at out + f*out_stride
     size_t out_stride;
     unsigned nbits, endstate;
+    const unsigned* endstates;  // per-frame end states (device, [n_frames]) or nullptr: use `endstate` for all
     int* results;               // device [n_frames] or nullptr
 };
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st);
+// best[f] = index of the smallest path metric of frame f (ties: lowest state); ka9q modular metrics are compared
+// as (int8) distances from state 0, s16 metrics as signed values
+cudaError_t launch_best_state(const CodecParams& c, const uint16_t* metrics, unsigned* best, int n_frames, cudaStream_t st);
 
 // ---- depuncturing front-end (depuncture.cu) -------------------------------------------------------------
 constexpr int MAX_PUNCTURE_LEN = 256;

@@ -82,6 +82,7 @@ def load_library():
         "b200v_batch_chainback_dev": (i32, [vp, vp, sz, u32, u32]),
         "b200v_batch_chainback": (i32, [vp, vp, sz, u32, u32]),
         "b200v_batch_chainback_results": (i32, [vp, vp]),
+        "b200v_batch_chainback_best_dev": (i32, [vp, vp, sz, u32, vp]),
         "b200v_batch_decode": (i32, [vp, vp, vp, u32]),
         "b200v_batch_decode_dev": (i32, [vp, vp, sz, vp, sz, u32]),
         "b200v_batch_sync": (i32, [vp]),
@@ -119,7 +120,7 @@ EXPORTED_SYMBOLS = [
     "b200v_codec_symbol_bytes", "b200v_codec_metric_bytes", "b200v_batch_create", "b200v_batch_destroy",
     "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_init",
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
-    "b200v_batch_chainback_results", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_batch_sync", "b200v_batch_get_decisions",
+    "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_batch_sync", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
     "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_shard_range", "b200v_sharded_create",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
@@ -214,6 +215,10 @@ class BatchDecoder:
 
     def chainback_dev(self, d_out, frame_stride_bytes, total_bits, endstate=0):
         _check(self.lib.b200v_batch_chainback_dev(self.h, _ptr(d_out), frame_stride_bytes, total_bits, endstate))
+
+    def chainback_best_dev(self, d_out, out_stride, nbits, d_best=None):
+        """Traceback from every frame's best state (unterminated streams)."""
+        _check(self.lib.b200v_batch_chainback_best_dev(self.h, _ptr(d_out), out_stride, nbits, _ptr(d_best)))
 
     def decode_dev(self, d_syms, sym_stride, d_out, out_stride, nbits):
         """init + update + chainback with device buffers (b200v_batch_decode_dev); asynchronous."""

@@ -438,3 +438,69 @@ def test_wy_u16_out_of_range_symbols_take_the_generic_family(name):
                 assert np.array_equal(dec.metrics(f), q.metrics()), (expect_variant, f)
                 assert np.array_equal(out[f], qo), (expect_variant, f)
                 q.close()
+
+
+@pytest.mark.parametrize("name", ["wy_sse_u8_k7r2", "wy_sse_u8_k9r4", "wy_sse_u8_k15r6"])
+def test_wy_hard8_config(name):
+    """b200v_wy_config = main.cpp's hard8 config (src/viterbi_configs.h:52-65): symbols +-1, tight thresholds."""
+    from test_oracle import _hard8
+    codec, K, R = CASES[name]
+    c = _hard8(o.codec_by_name(name))
+    nbytes = 8 if K == 15 else 64
+    T = nbytes * 8 + K - 1
+    rng = np.random.default_rng(88)
+    syms = np.where(rng.random((4, T * R)) < 0.5, 1, -1).astype(np.int8)
+    syms[3, ::3] = 0
+    cfg = kv.WyConfig(1, -1, c.max_error, c.init_start, c.init_other, c.renorm_threshold)
+    with kv.BatchDecoder(codec, T, 4, K=K, R=R, wy_config=cfg) as dec:
+        for v in variants(dec):
+            dec.reset()
+            dec.set_variant(v)
+            out = dec.decode(syms, nbytes * 8)
+            for f in range(4):
+                q = o.Oracle(c, T)
+                qo, qd = q.decode(syms[f], nbytes * 8)
+                assert np.array_equal(dec.decisions(f, 0, T), qd), (v, f)
+                assert np.array_equal(dec.metrics(f), q.metrics()), (v, f)
+                assert np.array_equal(out[f], qo), (v, f)
+                q.close()
+
+
+@pytest.mark.parametrize("name", ["ka9q27", "spiral29", "ka9q615", "wy_sse_u16_k7r2", "ka9q29"])
+def test_best_state_traceback_of_unterminated_streams(name):
+    """b200v_batch_chainback_best_dev: no tail, every frame traced from its own smallest path metric. Checked
+    against the oracle's metrics (argmin, ties to the lowest state; modular metrics as int8 distances from state 0)
+    and the oracle's chainback from that state; at low noise the decoded bits are the transmitted ones."""
+    import torch
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes, n_frames = (6, 3) if K == 15 else (40, 9)
+    T = nbytes * 8                                     # unterminated: only the data bits' steps are fed
+    nbits = T - (K - 1)
+    data, syms = make_batch(c, n_frames, nbytes, 0.3, seed=31)
+    syms = np.ascontiguousarray(syms[:, :T * R])
+    with kv.BatchDecoder(codec, T + K - 1, n_frames, K=K, R=R) as dec:
+        dec.reset()
+        dec.update(syms)
+        d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
+        d_best = torch.zeros(n_frames, dtype=torch.int32, device="cuda")
+        dec.chainback_best_dev(d_out, nbytes, nbits, d_best)
+        dec.sync()
+        out = d_out.cpu().numpy().reshape(n_frames, nbytes)
+        best = d_best.cpu().numpy()
+        with pytest.raises(kv.B200ViterbiError):
+            dec.chainback_best_dev(d_out, nbytes, nbits - 8, d_best)
+    for f in range(n_frames):
+        q = o.Oracle(c, T + K - 1)
+        q.init(0)
+        q.update(syms[f], T)
+        m = q.metrics().astype(np.int64)
+        if name in ("ka9q27", "ka9q29"):
+            m = ((m - m[0] + 128) % 256) - 128
+        assert int(best[f]) == int(np.argmin(m)), f
+        want = q.chainback(nbits, int(best[f]))
+        nb = (nbits + 7) // 8
+        assert np.array_equal(out[f, :nb], want), f
+        full = nbits // 8
+        assert np.array_equal(out[f, :full - 1], data[f, :full - 1]), f      # low noise: all but the freshest bits
+        q.close()

@@ -144,3 +144,36 @@ def test_channel_noiseless_levels():
         assert set(np.unique(syms).tolist()) == {lo, hi}
         bits = o.encode_bits(c, data)
         assert np.array_equal(syms == hi, bits == 1)
+
+
+def _hard8(c):
+    """src/viterbi_configs.h:52-65 (hard8): symbols +-1, max error 2R, margin 3x."""
+    c.soft_hi, c.soft_lo = 1, -1
+    c.max_error = 2 * c.R
+    c.init_start, c.init_other = 0, 3 * c.max_error
+    c.renorm_threshold = 255 - 3 * c.max_error
+    return c
+
+
+@pytest.mark.parametrize("name", ["wy_sse_u8_k7r2", "wy_avx_u8_k9r4", "wy_sse_u8_k15r6"])
+def test_oracle_matches_reference_with_the_hard8_config(name):
+    """The williamyang decoders take a numeric config; pin the restatement on main.cpp's other config too."""
+    if not o.ref_available():
+        pytest.skip("oracle/_ref not built")
+    c = _hard8(o.codec_by_name(name))
+    nbytes = 6 if c.K == 15 else 40
+    T = nbytes * 8 + c.K - 1
+    rng = np.random.default_rng(8)
+    o.ref_lib().kvref_wy_set_config_kind(1)
+    try:
+        r = o.Ref(name, T)
+    finally:
+        o.ref_lib().kvref_wy_set_config_kind(0)
+    q = o.Oracle(c, T)
+    for trial in range(3):
+        syms = rng.integers(-1, 2, T * c.R).astype(np.int8) if trial else np.where(rng.random(T * c.R) < 0.5, 1, -1).astype(np.int8)
+        ro, rd = r.decode(syms, nbytes * 8)
+        qo, qd = q.decode(syms, nbytes * 8)
+        assert np.array_equal(rd, qd) and np.array_equal(ro, qo)
+        assert np.array_equal(r.metrics(), q.metrics())
+    r.close(); q.close()
