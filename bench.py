@@ -343,8 +343,15 @@ def run_b200_arm(args):
     bytes_per_step_frame = R * sym_bytes + S / 8.0
     achieved = frames * T * bytes_per_step_frame / (upd * 1e-3) / 1e9
     lane_ops = frames * T * 4.0 * S                      # 4*S integer lane-ops per step
+    traffic, traffic_src = None, None
+    try:     # DRAM bytes per launch as ncu measured them (profiles/ncu_traffic.json: per frame-step, scaled to this launch)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.codec)
+        if tr:
+            traffic, traffic_src = tr["bytes_per_frame_step"] * frames * T, tr["capture"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                "traffic": None, "kernel": "update", "kernel_ms": upd, "chainback_ms": cb,
+                "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": frames * T * bytes_per_step_frame, "kernel": "update", "kernel_ms": upd, "chainback_ms": cb,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                 "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "note": "4*S integer lane-ops per trellis step"}}
 
