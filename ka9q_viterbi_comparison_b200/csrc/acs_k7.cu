@@ -192,8 +192,13 @@ __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7
     if constexpr (P < NB - 1) {
         constexpr int DELTA = CODE::cw(1 << P);            // lane 1 holds butterfly j | (1 << P)
         uint32_t W[NCW], Wc[NCW];
+        // ka9q / spiral: the complement is exactly C - bm (bm <= C), so the packed complement is one packed subtract
+        constexpr bool EXACT_COMPLEMENT = (POLICY == P_KA9Q_U8_MOD || POLICY == P_SPIRAL_R2 || POLICY == P_SPIRAL_R4);
 #pragma unroll
-        for (int c = 0; c < NCW; c++) { W[c] = pack2(bm[c], bm[c ^ DELTA]); Wc[c] = pack2(cm[c], cm[c ^ DELTA]); }
+        for (int c = 0; c < NCW; c++) {
+            W[c] = bm[c] + bm[c ^ DELTA] * 65536u;
+            Wc[c] = EXACT_COMPLEMENT ? (uint32_t)a.C * 0x10001u - W[c] : cm[c] + cm[c ^ DELTA] * 65536u;
+        }
         PairLoop<POLICY, CODE, P, 0>::run(w, W, Wc, clamp, a, acc0, acc1);
     } else {
         // in-register butterflies: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
