@@ -73,6 +73,10 @@ struct Cfg {
     static constexpr int SB = (POLICY == P_WY_U16) ? 2 : 1;     // bytes per input symbol
     // rebase the lanes when their minimum exceeds TH: window = TH + metric spread + two branch metrics < 2^16
     static constexpr unsigned TH = (TOP == 65535) ? 4096u : 16384u;
+    // 16-bit policies trigger their renormalisation rarely (threshold >> one branch metric): after a checked step
+    // the next `skip` steps provably cannot trigger (state 0 gains at most one branch metric per step), so those
+    // steps run without the frame-wide minimum and its barrier. Block-uniform only when a frame owns the block.
+    static constexpr bool DEFER = (TOP == 65535) && TPF >= 32;
     static_assert(NXB >= 3, "at least 4 threads per frame");
     static_assert(TPF <= 4 || NXB + 1 >= 10, "exchange swizzle is written for K=9 and K=15");
 };
@@ -205,6 +209,8 @@ __device__ __forceinline__ uint32_t local_min(const uint32_t (&w)[NREG]) {
 struct FrameState {
     int base;          // tb = w + base
     uint32_t clamp;    // packed clamp operand of the saturating adds
+    int skip;          // DEFER: steps that need no trigger check (uniform over the frame)
+    int skip_cap;      // DEFER: bound that keeps min(w) + spread inside the 16-bit window between rebases
 };
 
 template <int POLICY, class CF>
@@ -226,7 +232,14 @@ __device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint
         for (int i = 0; i < NREG; i++) w[i] -= sub;      // every lane >= gmin: no borrow between lanes
         fs.base += (int)gmin;
     }
-    set_clamp<POLICY, CF>(fs, bm_cap<POLICY, CF::TOP>(a.C));
+    const int bmx = bm_cap<POLICY, CF::TOP>(a.C);
+    set_clamp<POLICY, CF>(fs, bmx);
+    if (CF::DEFER) {
+        // new[0] <= old[0] + bm_max: no trigger for the next (thr - tb0) / bm_max steps (">=" trigger: thr - 1)
+        const int tb0n = need ? (int)g0 - (int)gmin : tb0;
+        const int room = thr - (CF::strict ? 0 : 1) - tb0n;
+        fs.skip = room > 0 ? min(room / bmx, fs.skip_cap) : 0;
+    }
 }
 
 // ---- butterflies of one step in phase P -------------------------------------------------------------------
@@ -474,6 +487,17 @@ __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const 
         }
         return;
     }
+    if constexpr (CF::DEFER) {
+        if (fs.skip > 0) {
+            fs.skip--;
+            if (EXCH) {
+                exchange_store<CF>(w, met_addr, tx);
+                __syncthreads();
+                exchange_load<CF>(w, met_addr, tx);
+            }
+            return;
+        }
+    }
     const uint32_t lm = local_min(w);
     const uint32_t w0 = w[0];
     if (EXCH) {
@@ -521,6 +545,11 @@ acs_grp_kernel(const GrpArgs a) {
     FrameState fs;
     fs.base = 0;
     fs.clamp = 0;
+    fs.skip = 0;
+    {   // min(w) <= TH + skip * bm_max between rebases; window: that + (K + 1) branch metrics of spread and headroom
+        const int bmx = max(bm_cap<POLICY, CF::TOP>(a.C), 1);
+        fs.skip_cap = max(0, min(10, (65535 - (int)CF::TH - (CF::K + 1) * bmx) / bmx - 1));
+    }
     if (!CF::modular) {   // bring the lanes down to the bottom of the 16-bit window
         uint32_t gmin, g0;
         frame_min<CF>(local_min(w), w[0], s_red, rpar, tid, gmin, g0);

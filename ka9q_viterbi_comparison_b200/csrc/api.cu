@@ -272,6 +272,7 @@ extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
         return fail(B200V_ERR_STATE, "the kernel family can only change right after init (decision layouts differ)");
     if (variant == 1 && h->generic_ok) { h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
     if (variant == 2 && h->has_fast) { h->variant = 2; h->layout = h->fast_layout; return B200V_OK; }
+    if (variant == 3 && k7_warp_supported(h->c)) { h->variant = 3; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
     return fail(B200V_ERR_ARG, "kernel family %d is not available for this instance", variant);
 }
 extern "C" int b200v_batch_get_variant(const b200v_batch* h) { return h ? h->variant : 0; }
@@ -353,7 +354,8 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
         a.c = c; a.syms = d_syms; a.sym_stride = stride; a.nsteps = nsteps; a.step0 = step0;
         a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
         a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
-        CUDA_TRY(launch_acs_generic(a, st));
+        if (h->variant == 3) CUDA_TRY(launch_acs_k7_warp(a, st));
+        else CUDA_TRY(launch_acs_generic(a, st));
         h->launches++;
     }
     return B200V_OK;

@@ -25,6 +25,10 @@ struct GenericPlan { int threads_per_frame, frames_per_block, smem_bytes; };
 GenericPlan generic_plan(const CodecParams& c);
 cudaError_t launch_acs_generic(const GenericArgs& a, cudaStream_t st);
 
+// ---- K=7 warp-per-frame kernel (acs_k7_warp.cu): the alternative design, kept for the measured comparison ----
+bool k7_warp_supported(const CodecParams& c);
+cudaError_t launch_acs_k7_warp(const GenericArgs& a, cudaStream_t st);
+
 // metrics[f][s] = init_other, metrics[f][start] = init_start (all families share this buffer format)
 cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecParams& c, int starting_state,
                                 cudaStream_t st);

@@ -46,7 +46,7 @@ def variants(dec):
     """Kernel families available for this instance (1 = generic always; 2 = specialised when present)."""
     out = []
     dec.reset()
-    for v in (1, 2):
+    for v in (1, 2, 3):
         try:
             dec.set_variant(v)
             out.append(v)
