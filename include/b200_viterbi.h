@@ -150,7 +150,7 @@ int b200v_batch_decode_dev(b200v_batch* h, const void* d_syms, size_t sym_stride
 int b200v_batch_sync(b200v_batch* h);
 
 /* ---- introspection (parity tests, SURVEY 8b "b200v_batch_get_decisions") ---- */
-/* Canonical decision vectors of one frame: S/8 bytes per step, bit n of the little-endian vector is the
+/* Canonical decision vectors of one frame: max(S/8, 1) bytes per step, bit n of the little-endian vector is the
  * decision of new state n (the layout every reference decoder uses). Host output buffer. */
 int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, int nsteps, uint8_t* out);
 /* Current path metrics of one frame: S elements of b200v_codec_metric_bytes() each. Host buffer. */

@@ -625,6 +625,7 @@ static cudaError_t launch_one(const GrpArgs& a, cudaStream_t st) {
 
 using CodeK9R2 = Code<9, 2, 0x1af, 0x11d, 0, 0, 0, 0>;                                   // src/main.cpp:386
 using CodeK9R4 = Code<9, 4, 501, 441, 331, 315, 0, 0>;                                   // src/main.cpp:396
+using CodeIS95 = Code<9, 2, 491, 369, 0, 0, 0, 0>;       // williamyang_viterbi_lib/examples/helpers/common_codes.h:28 (CDMA IS-95A)
 using CodeK15R6 = Code<15, 6, 042631, 047245, 056507, 073363, 077267, 064537>;           // src/main.cpp:405
 
 template <class CODE>
@@ -636,7 +637,7 @@ static bool same_code(const CodecParams& c) {
 }
 
 enum Instance { I_NONE = -1, I_KA9Q29, I_KA9Q615, I_SPIRAL615, I_WY8_K15R6, I_SPIRAL29, I_WY8_K9R2, I_SPIRAL49, I_WY8_K9R4,
-                I_WY16_K15R6, I_WY16_K9R2, I_WY16_K9R4 };
+                I_WY16_K15R6, I_WY16_K9R2, I_WY16_K9R4, I_WY8_IS95, I_WY16_IS95 };
 
 static int find_instance(const CodecParams& c) {
     if (same_code<CodeK15R6>(c)) {
@@ -649,6 +650,9 @@ static int find_instance(const CodecParams& c) {
         if (c.policy == P_SPIRAL_R2) return I_SPIRAL29;
         if (c.policy == P_WY_U8) return I_WY8_K9R2;
         if (c.policy == P_WY_U16) return I_WY16_K9R2;
+    } else if (same_code<CodeIS95>(c)) {
+        if (c.policy == P_WY_U8) return I_WY8_IS95;
+        if (c.policy == P_WY_U16) return I_WY16_IS95;
     } else if (same_code<CodeK9R4>(c)) {
         if (c.policy == P_SPIRAL_R4) return I_SPIRAL49;
         if (c.policy == P_WY_U8) return I_WY8_K9R4;
@@ -691,6 +695,8 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
     a.frame0 = frame0; a.count = count;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1;
     switch (grp::find_instance(c)) {
+    case grp::I_WY8_IS95: return grp::launch_one<P_WY_U8, grp::CodeIS95>(a, st);
+    case grp::I_WY16_IS95: return grp::launch_one<P_WY_U16, grp::CodeIS95>(a, st);
     case grp::I_KA9Q29: return grp::launch_one<P_KA9Q_U8_MOD, grp::CodeK9R2>(a, st);
     case grp::I_KA9Q615: return grp::launch_one<P_KA9Q_S16_615, grp::CodeK15R6>(a, st);
     case grp::I_SPIRAL615: return grp::launch_one<P_SPIRAL_615, grp::CodeK15R6>(a, st);

@@ -389,7 +389,8 @@ static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
 
 using CodeK7R2 = Code<2, 0x6d, 0x4f, 0, 0>;       // src/main.cpp:367 (Voyager)
 using CodeK7R4 = Code<4, 121, 117, 91, 111>;      // src/main.cpp:377
-using CodeK7R3 = Code<3, 91, 117, 121, 0>;        // williamyang_viterbi_lib/examples/helpers/common_codes.h (LTE)
+using CodeK7R3 = Code<3, 91, 117, 121, 0>;        // williamyang_viterbi_lib/examples/helpers/common_codes.h:26 (LTE)
+using CodeDAB = Code<4, 109, 79, 83, 109>;        // common_codes.h:27 (DAB Radio; run_punctured_decoder.cpp's code)
 
 // index of the instantiation matching (policy, R, poly), or -1
 static int find_instance(const CodecParams& c) {
@@ -404,6 +405,10 @@ static int find_instance(const CodecParams& c) {
         if (c.policy == P_SPIRAL_R4) return 3;
         if (c.policy == P_WY_U8) return 4;
         if (c.policy == P_WY_U16) return 7;
+    }
+    if (c.R == 4 && c.poly[0] == 109 && c.poly[1] == 79 && c.poly[2] == 83 && c.poly[3] == 109) {
+        if (c.policy == P_WY_U8) return 9;
+        if (c.policy == P_WY_U16) return 10;
     }
     if (c.R == 3 && c.poly[0] == 91 && c.poly[1] == 117 && c.poly[2] == 121 && c.policy == P_WY_U8) return 5;
     if (c.R == 3 && c.poly[0] == 91 && c.poly[1] == 117 && c.poly[2] == 121 && c.policy == P_WY_U16) return 8;
@@ -449,6 +454,8 @@ cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_str
     case 6: return k7::launch_one<P_WY_U16, k7::CodeK7R2>(a, st);
     case 7: return k7::launch_one<P_WY_U16, k7::CodeK7R4>(a, st);
     case 8: return k7::launch_one<P_WY_U16, k7::CodeK7R3>(a, st);
+    case 9: return k7::launch_one<P_WY_U8, k7::CodeDAB>(a, st);
+    case 10: return k7::launch_one<P_WY_U16, k7::CodeDAB>(a, st);
     default: return cudaErrorInvalidValue;
     }
 }

@@ -588,7 +588,7 @@ extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, i
         return fail(B200V_ERR_ARG, "frame/step range out of bounds");
     CUDA_TRY(cudaSetDevice(h->device));
     const int S = h->c.S;
-    const size_t nb = (size_t)S / 8;
+    const size_t nb = S >= 8 ? (size_t)S / 8 : 1;     // K = 3: four states still take one byte per step
     memset(out, 0, nb * nsteps);
     if (h->layout == DL_CANONICAL) {
         const uint32_t* src = (const uint32_t*)h->d_dec + ((size_t)frame * h->dec_rows + step0) * h->row_words;

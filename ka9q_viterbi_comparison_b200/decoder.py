@@ -258,7 +258,7 @@ class BatchDecoder:
         return out
 
     def decisions(self, frame, step0, nsteps):
-        out = np.zeros((nsteps, self.S // 8), dtype=np.uint8)
+        out = np.zeros((nsteps, max(self.S // 8, 1)), dtype=np.uint8)
         _check(self.lib.b200v_batch_get_decisions(self.h, frame, step0, nsteps, out.ctypes.data))
         return out
 

@@ -105,3 +105,5 @@ WY_ALL(9, 2)
 WY_ALL(9, 4)
 WY_ALL(15, 6)
 WY_ALL(24, 2)
+/* common_codes.h:24 "Basic K=5 R=1/2": the smallest K a SIMD decoder accepts (SSE u16; the others need K >= 6 or 7) */
+WY_VT(wy_sse_u16_k5r2, 5, 2, int16_t, uint16_t, ViterbiDecoder_SSE_u16)

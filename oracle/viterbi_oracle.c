@@ -108,6 +108,9 @@ int kvo_codec_by_name(kvo_codec* c, const char* name) {
 /* decoder instance                                                                                   */
 /* ------------------------------------------------------------------------------------------------ */
 
+/* canonical decision vector of one step: S bits, at least one byte (K = 3: S = 4) */
+static inline size_t row_bytes(int S) { return S >= 8 ? (size_t)S / 8 : 1; }
+
 struct kvo_decoder {
     kvo_codec c;
     int S;                 /* number of states 2^(K-1) */
@@ -132,7 +135,7 @@ kvo_decoder* kvo_create(const kvo_codec* c, int len) {
     d->cw = (uint8_t*)calloc((size_t)d->S / 2, 1);
     d->old_m = (int32_t*)malloc(sizeof(int32_t) * d->S);
     d->new_m = (int32_t*)malloc(sizeof(int32_t) * d->S);
-    d->dec = (uint8_t*)calloc((size_t)d->len, (size_t)d->S / 8);
+    d->dec = (uint8_t*)calloc((size_t)d->len, row_bytes(d->S));
     if (!d->branch || !d->cw || !d->old_m || !d->new_m || !d->dec) { kvo_destroy(d); return NULL; }
     const int spiral = c->policy == KVO_SPIRAL_R2 || c->policy == KVO_SPIRAL_R4 || c->policy == KVO_SPIRAL_615;
     for (int i = 0; i < c->R; i++) {
@@ -225,7 +228,7 @@ static int32_t branch_metric(const kvo_decoder* d, const int32_t* sym, unsigned 
 static void step(kvo_decoder* d, const int32_t* sym, uint8_t* row) {
     const kvo_codec* c = &d->c;
     const int S = d->S, H = S / 2;
-    memset(row, 0, (size_t)S / 8);
+    memset(row, 0, row_bytes(S));
     int32_t bmtab[1 << KVO_MAX_R];   /* the branch metric depends on j only through its code word */
     for (unsigned w = 0; w < (1u << c->R); w++) bmtab[w] = branch_metric(d, sym, w);
     for (int j = 0; j < H; j++) {
@@ -330,13 +333,13 @@ void kvo_update(kvo_decoder* d, const void* syms, int nsteps) {
             else sym[i] = ((const uint8_t*)syms)[k];
         }
         if (d->cursor >= d->len) return;
-        step(d, sym, d->dec + (size_t)d->cursor * (d->S / 8));
+        step(d, sym, d->dec + (size_t)d->cursor * row_bytes(d->S));
         d->cursor++;
     }
 }
 
 void kvo_get_decisions(kvo_decoder* d, int step0, int nsteps, uint8_t* out) {
-    memcpy(out, d->dec + (size_t)step0 * (d->S / 8), (size_t)nsteps * (d->S / 8));
+    memcpy(out, d->dec + (size_t)step0 * row_bytes(d->S), (size_t)nsteps * row_bytes(d->S));
 }
 
 void kvo_get_metrics(kvo_decoder* d, void* out) {
@@ -347,7 +350,7 @@ void kvo_get_metrics(kvo_decoder* d, void* out) {
 }
 
 static inline int dec_bit(const kvo_decoder* d, size_t row, unsigned state) {
-    return (d->dec[row * (size_t)(d->S / 8) + (state >> 3)] >> (state & 7)) & 1;
+    return (d->dec[row * row_bytes(d->S) + (state >> 3)] >> (state & 7)) & 1;
 }
 
 int kvo_chainback(kvo_decoder* d, uint8_t* data, unsigned nbits, unsigned endstate) {

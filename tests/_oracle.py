@@ -80,6 +80,26 @@ def codec_by_name(name, poly=None):
     return c
 
 
+def codec_wy(width, K, R, poly):
+    """williamyang policy (width 8 or 16) for any (K, R, polynomials), e.g. the common_codes.h entries."""
+    c = KvoCodec()
+    if oracle_lib().kvo_codec_defaults(C.byref(c), 6 if width == 8 else 7, K, R) != 0:
+        raise ValueError((width, K, R))
+    assert len(poly) == R
+    for i in range(MAX_R):
+        c.poly[i] = int(poly[i]) if i < R else 0
+    return c
+
+
+# williamyang_viterbi_lib/examples/helpers/common_codes.h:23-30
+COMMON_CODES = [
+    ("Basic K=3 R=1/2", 3, 2, [0b111, 0b101]), ("Basic K=5 R=1/2", 5, 2, [0b10111, 0b11001]),
+    ("Voyager", 7, 2, [109, 79]), ("LTE", 7, 3, [91, 117, 121]), ("DAB Radio", 7, 4, [109, 79, 83, 109]),
+    ("CDMA IS-95A", 9, 2, [491, 369]), ("CDMA 2000", 9, 4, [501, 441, 331, 315]),
+    ("Cassini", 15, 6, [17817, 20133, 23879, 30451, 32439, 26975]),
+]
+
+
 def sym_dtype(codec):
     return {6: np.int8, 7: np.int16}.get(codec.policy, np.uint8)
 
@@ -126,7 +146,7 @@ class Oracle(_Decoder):
         return (out, rc) if return_code else out
 
     def decisions(self, step0, nsteps):
-        out = np.zeros((nsteps, self.S // 8), dtype=np.uint8)
+        out = np.zeros((nsteps, max(self.S // 8, 1)), dtype=np.uint8)
         self.lib.kvo_get_decisions(self.h, step0, nsteps, out.ctypes.data)
         return out
 
@@ -188,8 +208,10 @@ class Ref(_Decoder):
     """The compiled, unmodified reference decoder `name` (standard polys only: the reference keeps its
     branch table in a process-global that the first create() fills)."""
 
-    def __init__(self, name, len_steps):
-        codec = codec_by_name(name)
+    def __init__(self, name, len_steps, codec=None):
+        """`codec`: a williamyang codec with its own polynomials (their branch table is per instance)."""
+        assert codec is None or name.startswith("wy_")
+        codec = codec or codec_by_name(name)
         super().__init__(codec, len_steps)
         vt = ref_lib().kvref_find(name.encode())
         if not vt:
@@ -212,7 +234,7 @@ class Ref(_Decoder):
         return (out, rc) if return_code else out
 
     def decisions(self, step0, nsteps):
-        out = np.zeros((nsteps, self.S // 8), dtype=np.uint8)
+        out = np.zeros((nsteps, max(self.S // 8, 1)), dtype=np.uint8)
         self.vt.get_decisions(self.h, step0, nsteps, out.ctypes.data)
         return out
 

@@ -504,3 +504,36 @@ def test_best_state_traceback_of_unterminated_streams(name):
         full = nbits // 8
         assert np.array_equal(out[f, :full - 1], data[f, :full - 1]), f      # low noise: all but the freshest bits
         q.close()
+
+
+@pytest.mark.parametrize("code", o.COMMON_CODES, ids=[c[0].replace(" ", "_") for c in o.COMMON_CODES])
+@pytest.mark.parametrize("width", [8, 16])
+def test_common_codes(code, width):
+    """Every entry of the williamyang library's code list (examples/helpers/common_codes.h:23-30), both metric
+    widths, every kernel family the instance offers; K >= 7 entries must be served by a specialised family."""
+    _, K, R, poly = code
+    c = o.codec_wy(width, K, R, poly)
+    nbytes = 16 if K == 15 else 96
+    T = nbytes * 8 + K - 1
+    n_frames = 2 if K == 15 else 9
+    data, syms = make_batch(c, n_frames, nbytes, 0.8, seed=0xC0DE)
+    refs = []
+    for f in range(n_frames):
+        q = o.Oracle(c, T)
+        q.init(0)
+        q.update(syms[f], T)
+        refs.append((q.decisions(0, T), q.metrics(), q.chainback(nbytes * 8, 0)))
+        q.close()
+    with kv.BatchDecoder(kv.WY_U8 if width == 8 else kv.WY_U16, T, n_frames, K=K, R=R, poly=poly) as dec:
+        assert dec.variant == (2 if K >= 7 else 1), "kernel family chosen for this code"
+        for v in variants(dec):
+            dec.reset()
+            dec.set_variant(v)
+            dec.reset()
+            dec.update(syms)
+            out = dec.chainback(nbytes * 8)
+            for f in range(n_frames):
+                qd, qm, qo = refs[f]
+                assert np.array_equal(dec.decisions(f, 0, T), qd), f"v{v} frame {f}: decisions"
+                assert np.array_equal(dec.metrics(f), qm), f"v{v} frame {f}: metrics"
+                assert np.array_equal(out[f], qo), f"v{v} frame {f}: decoded bytes"

@@ -177,3 +177,31 @@ def test_oracle_matches_reference_with_the_hard8_config(name):
         assert np.array_equal(rd, qd) and np.array_equal(ro, qo)
         assert np.array_equal(r.metrics(), q.metrics())
     r.close(); q.close()
+
+
+# common_codes.h entries that main.cpp does not benchmark: other polynomials (DAB, IS-95A) and the smallest K a
+# SIMD decoder accepts (K=5, SSE u16 only). The williamyang decoders build their branch table per instance, so the compiled
+# reference can be asked for them directly.
+COMMON_EXTRA = [("k5r2", 5, 2, [0b10111, 0b11001], ("wy_sse_u16",)),
+                ("k7r4", 7, 4, [109, 79, 83, 109], ("wy_sse_u8", "wy_avx_u8", "wy_sse_u16", "wy_avx_u16")),
+                ("k9r2", 9, 2, [491, 369], ("wy_sse_u8", "wy_avx_u8", "wy_sse_u16", "wy_avx_u16"))]
+
+
+@pytest.mark.skipif(not o.ref_available(), reason="oracle/_ref/libkvref.so not built")
+@pytest.mark.parametrize("kr,K,R,poly,decoders", COMMON_EXTRA, ids=[c[0] for c in COMMON_EXTRA])
+def test_oracle_matches_reference_on_common_codes(kr, K, R, poly, decoders):
+    nbytes = 64
+    T = nbytes * 8 + K - 1
+    for prefix in decoders:
+        c = o.codec_wy(8 if prefix.endswith("u8") else 16, K, R, poly)
+        for sigma in (0.0, 0.7, 1.3):
+            data, syms = o.make_frame(c, nbytes, sigma, seed=0xC0DE, frame=3)
+            r, q = o.Ref(f"{prefix}_{kr}", T, codec=c), o.Oracle(c, T)
+            ro, rd = r.decode(syms, nbytes * 8)
+            qo, qd = q.decode(syms, nbytes * 8)
+            assert np.array_equal(rd, qd), (prefix, sigma, "decision vectors differ")
+            assert np.array_equal(r.metrics(), q.metrics()), (prefix, sigma, "metrics differ")
+            assert np.array_equal(ro, qo), (prefix, sigma, "decoded bytes differ")
+            if sigma == 0.0:
+                assert np.array_equal(ro, data)
+            r.close(); q.close()
