@@ -111,6 +111,7 @@ struct K7Args {
     int frame0, count;             // frames [frame0, frame0 + count) of the n_frames-wide layout
     int C, thr, soft_hi, soft_lo;
     int one, neg1;                 // 1 and -1, opaque to ptxas: multipliers that keep plain adds on the FMA pipe
+    int zero;                      // 0, opaque to ptxas: third operand that keeps an add on the ALU pipe (IADD3)
 };
 
 // ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
@@ -123,7 +124,17 @@ struct PairLoop {
         constexpr int c = CODE::cw(logical_of(P, iA << 1));
         const uint32_t A = w[iA], B = w[iB];
         if (Arith<POLICY>::modular) {      // decision = (lo path > hi path), tie -> 0 (viterbi27_sse2.cpp:155-158)
-            const uint32_t m0 = A + W[c], m1 = B + Wc[c], m2 = A + Wc[c], m3 = B + W[c];
+#ifndef K7_ALU_ADDS
+#define K7_ALU_ADDS 32
+#endif
+            // pipe balance: ptxas emits two-input adds as VIADD / IMAD.IADD, which ncu attributes to the FMA-heavy
+            // pipe (82 % busy, the binding pipe of this kernel: profiles/r01b_k7_ka9q27.txt); the lo-path adds are
+            // forced onto the ALU pipe as IADD3 (K7_ALU_ADDS of the 64 adds of a step; measured 0 / 16 / 32:
+            // 16.75 / 16.07 / 15.88 ms per 1 Mi frames). Keep the statement order: ptxas spills predicates otherwise.
+            const uint32_t m0 = (KK < K7_ALU_ADDS) ? add_alu(A, W[c], (uint32_t)a.zero) : A + W[c];
+            const uint32_t m1 = B + Wc[c];
+            const uint32_t m2 = (KK + 16 < K7_ALU_ADDS) ? add_alu(A, Wc[c], (uint32_t)a.zero) : A + Wc[c];
+            const uint32_t m3 = B + W[c];
             w[iA] = min_acc<KK, 16 + KK, true>(m0, m1, acc0);
             w[iB] = min_acc<KK, 16 + KK, true>(m2, m3, acc1);
         } else {
@@ -131,16 +142,19 @@ struct PairLoop {
             // <= clamp, and a doubly saturated butterfly still decides "hi" because hi == clamp); the lo-path adds
             // are plain adds on the FMA pipe. decision = (min == hi path) = (lo - hi >= 0), tie -> 1
             // (spiral27.cpp:178-181): bit 15 of each lane of lo + 0x8000 - hi (|lo - hi| < 2^15), also on the FMA
-            // pipe; the two bits are shifted into the decision word (pair KK ends at bits KK / 16+KK after the
-            // 16 pairs). No predicates: ptxas spilled them in the predicated form of this loop.
+            // pipe. No predicates: ptxas spilled them in the predicated form of this loop.
             const uint32_t m0 = add_fma(A, (uint32_t)a.one, W[c]), m1 = __viaddmin_u16x2(B, Wc[c], clamp);
             const uint32_t m2 = add_fma(A, (uint32_t)a.one, Wc[c]), m3 = __viaddmin_u16x2(B, W[c], clamp);
             const uint32_t x0 = add_fma(m1, (uint32_t)a.neg1, add_fma(m0, (uint32_t)a.one, 0x80008000u));
             const uint32_t x1 = add_fma(m3, (uint32_t)a.neg1, add_fma(m2, (uint32_t)a.one, 0x80008000u));
             w[iA] = __vminu2(m1, m0);
             w[iB] = __vminu2(m3, m2);
-            acc0 = (acc0 >> 1) | (x0 & 0x80008000u);
-            acc1 = (acc1 >> 1) | (x1 & 0x80008000u);
+            // four decisions (A lane 0, A lane 1, B lane 0, B lane 1) as 0x00 / 0xff bytes: PRMT replicates the sign
+            // bit of bytes 1 and 3 of x0 and x1; one LOP3 masks bit KK & 7 of each byte into the word of group KK
+            // (acs_k7.cuh: bytewise packing). Two ALU instructions per four decisions.
+            const uint32_t r = sign_bytes(x0, x1);
+            uint32_t& acc = (KK < 8) ? acc0 : acc1;
+            acc |= r & (0x01010101u << (KK & 7));
         }
         PairLoop<POLICY, CODE, P, KK + 1>::run(w, W, Wc, clamp, a, acc0, acc1);
     }
@@ -155,7 +169,7 @@ struct PairLoop<POLICY, CODE, P, 16> {
 template <int POLICY, class CODE, int I>
 struct InRegLoop {
     __device__ __forceinline__ static void run(uint32_t (&w)[NW], const uint32_t* bm, const uint32_t* cm,
-                                               uint32_t clamp, uint32_t& acc0, uint32_t& acc1) {
+                                               uint32_t clamp, uint32_t& acc0, uint32_t& acc1, uint32_t xe = 0) {
         constexpr int c = CODE::cw(I);
         const uint32_t x = w[I];
         const uint32_t ma = Arith<POLICY>::add(x, bm[c] * 0x10001u, clamp);   // (m0, m3)
@@ -164,17 +178,19 @@ struct InRegLoop {
         const uint32_t hi_paths = __byte_perm(mb, ma, 0x7632);               // (m1, m3)
         uint32_t& acc = (I < 16) ? acc0 : acc1;
         if (Arith<POLICY>::modular) w[I] = min_acc<(I & 15), 16 + (I & 15), true>(lo_paths, hi_paths, acc);
-        else {      // same arithmetic decision as PairLoop; registers 0..15 fill acc0, 16..31 fill acc1, in order
+        else {      // same arithmetic decision as PairLoop; registers (I, I + 1) share one PRMT + LOP3 (bytewise packing)
             w[I] = __vminu2(hi_paths, lo_paths);
-            acc = (acc >> 1) | ((lo_paths + 0x80008000u - hi_paths) & 0x80008000u);
+            const uint32_t x = lo_paths + 0x80008000u - hi_paths;
+            if (I & 1) acc |= sign_bytes(xe, x) & (0x01010101u << ((I >> 1) & 7));
+            else xe = x;
         }
-        InRegLoop<POLICY, CODE, I + 1>::run(w, bm, cm, clamp, acc0, acc1);
+        InRegLoop<POLICY, CODE, I + 1>::run(w, bm, cm, clamp, acc0, acc1, xe);
     }
 };
 template <int POLICY, class CODE>
 struct InRegLoop<POLICY, CODE, NW> {
     __device__ __forceinline__ static void run(uint32_t (&)[NW], const uint32_t*, const uint32_t*, uint32_t,
-                                               uint32_t&, uint32_t&) {}
+                                               uint32_t&, uint32_t&, uint32_t) {}
 };
 
 // ---- one trellis step in phase P -------------------------------------------------------------------
@@ -443,7 +459,7 @@ cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_str
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
-    a.one = 1; a.neg1 = -1;
+    a.one = 1; a.neg1 = -1; a.zero = 0;
     switch (k7::find_instance(c)) {
     case 0: return k7::launch_one<P_KA9Q_U8_MOD, k7::CodeK7R2>(a, st);
     case 1: return k7::launch_one<P_SPIRAL_R2, k7::CodeK7R2>(a, st);

@@ -46,19 +46,28 @@ __host__ __device__ constexpr int compress_bit(int i, int pos) {
 }
 
 // Bit position (0..63) inside the per-step decision word of the decision for NEW logical state n produced by
-// a step executed in phase p. Decision word = acc0 | acc1 << 32 where, for p < 5, acc0 collects the A
-// registers (new even states) and acc1 the B registers (new odd states), k-th pair at bit k (lane 0) and
-// 16+k (lane 1); for p = 5, acc0 collects registers 0..15 and acc1 registers 16..31.
-__host__ __device__ constexpr int decision_bit_of(int p, int n) {
+// a step executed in phase p. Decision word = acc0 | acc1 << 32. Two packings:
+//  * bitwise (ka9q modular policy: each decision is a predicated OR of one constant bit): for p < 5, acc0 collects
+//    the A registers (new even states) and acc1 the B registers (new odd states), k-th pair at bit k (lane 0) and
+//    16+k (lane 1); for p = 5, acc0 collects registers 0..15 and acc1 registers 16..31.
+//  * bytewise (saturating policies: four decisions at a time leave a PRMT as 0x00/0xff bytes and are masked into
+//    the word with one LOP3): group g = pair k (p < 5) or register pair i >> 1 (p = 5) lands in word g >> 3 at
+//    bit g & 7 of byte {A lane 0, A lane 1, B lane 0, B lane 1} (p < 5) / {even register lane 0, lane 1, odd
+//    register lane 0, lane 1} (p = 5).
+__host__ __device__ constexpr int decision_bit_of(int p, int n, bool bytewise) {
     const int q = physical_of((p + 1) % NB, n);   // layout after the step
     const int lane = q & 1, i = q >> 1;
     if (p < NB - 1) {
         const int xb = NB - 2 - p;
-        const int is_b = (i >> xb) & 1;
-        return is_b * 32 + lane * 16 + compress_bit(i, xb);
+        const int is_b = (i >> xb) & 1, k = compress_bit(i, xb);
+        if (bytewise) return (k >> 3) * 32 + (is_b * 2 + lane) * 8 + (k & 7);
+        return is_b * 32 + lane * 16 + k;
     }
+    if (bytewise) return (i >> 4) * 32 + ((i & 1) * 2 + lane) * 8 + ((i >> 1) & 7);
     return (i >> 4) * 32 + lane * 16 + (i & 15);
 }
+// which packing a policy's kernel writes (policy ids: codec.h)
+__host__ __device__ constexpr bool decisions_bytewise(int policy) { return policy != 0 /* P_KA9Q_U8_MOD */; }
 
 // code word of butterfly j: bit i = parity((2j) & poly_i)
 __host__ __device__ constexpr int parity_of(unsigned x) {

@@ -628,7 +628,7 @@ extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, i
         for (int t = 0; t < nsteps; t++) {
             uint8_t* o = out + (size_t)t * nb;
             for (int n = 0; n < S; n++)
-                o[n >> 3] |= (uint8_t)(((rows[t] >> k7::decision_bit_of(phase[t], n)) & 1ull) << (n & 7));
+                o[n >> 3] |= (uint8_t)(((rows[t] >> k7::decision_bit_of(phase[t], n, k7::decisions_bytewise(h->c.policy))) & 1ull) << (n & 7));
         }
         return B200V_OK;
     }

@@ -58,7 +58,7 @@ __global__ void chainback_kernel(const ChainbackArgs a) {
 // at memory bandwidth instead of paying one DRAM latency per decoded bit.
 __global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a) {
     __shared__ uint8_t tab[k7::NB * k7::S];
-    fill_k7_table(tab);
+    fill_k7_table(tab, a.c.policy);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.count) return;
     const int f = a.frame0 + idx;

@@ -74,9 +74,10 @@ template <> struct DecisionReader<DL_GRP_INTERLEAVED> {
     }
 };
 
-__device__ __forceinline__ void fill_k7_table(uint8_t* tab) {
+__device__ __forceinline__ void fill_k7_table(uint8_t* tab, int policy) {
+    const bool bytewise = k7::decisions_bytewise(policy);
     for (int i = threadIdx.x; i < k7::NB * k7::S; i += blockDim.x)
-        tab[i] = (uint8_t)k7::decision_bit_of(i / k7::S, i % k7::S);
+        tab[i] = (uint8_t)k7::decision_bit_of(i / k7::S, i % k7::S, bytewise);
     __syncthreads();
 }
 

@@ -66,5 +66,20 @@ __device__ __forceinline__ uint32_t add_fma(uint32_t a, uint32_t one, uint32_t b
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
     return d;
 }
+// PRMT in its generic mode: selector nibbles with bit 3 set replicate the sign bit of the selected byte
+// (__byte_perm masks that bit away). sign_bytes(x0, x1) = {msb(x0.b1), msb(x0.b3), msb(x1.b1), msb(x1.b3)} as
+// 0x00 / 0xff bytes: the four bit-15 / bit-31 decisions of two packed differences.
+__device__ __forceinline__ uint32_t sign_bytes(uint32_t x0, uint32_t x1) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, 0xfdb9;" : "=r"(d) : "r"(x0), "r"(x1));
+    return d;
+}
+// a + b on the ALU pipe: a three-input add with an opaque zero stays an IADD3 (ptxas turns two-input adds into
+// VIADD / IMAD.IADD, both of which ncu attributes to the FMA-heavy pipe on B200)
+__device__ __forceinline__ uint32_t add_alu(uint32_t a, uint32_t b, uint32_t zero) {
+    uint32_t d;
+    asm("{\n\t.reg .u32 t;\n\tadd.u32 t, %1, %2;\n\tadd.u32 %0, t, %3;\n\t}" : "=r"(d) : "r"(a), "r"(b), "r"(zero));
+    return d;
+}
 
 }  // namespace b200v
