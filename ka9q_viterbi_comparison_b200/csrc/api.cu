@@ -560,7 +560,11 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
 // Device-pointer batch entry: init + update(frame_steps) + chainback(nbits) with symbols and output already in
 // HBM; asynchronous, on the instance's stream. Measured on the B200: running the HBM-bound chainback of one chunk
 // of frames beside the issue-bound update of the next (priority streams) is SLOWER than back-to-back whole-batch
-// launches (23.9 vs 20.5 ms for 1 Mi K=7 frames), so the three kernels simply follow each other.
+// launches (23.9 vs 20.5 ms for 1 Mi K=7 frames), and so is a single warp-specialised launch in which every block
+// updates 128 frames on four warps while a fifth warp traces back the frames of a block that finished one residency
+// earlier (ticket + release/acquire flags; bit-exact, but 40.4 vs 19.5 ms: one traceback warp per block is latency
+// bound at ~0.9 ms per 32 frames and holds the block's slot 4x longer than the update needs). So the three kernels
+// simply follow each other.
 extern "C" int b200v_batch_decode_dev(b200v_batch* h, const void* d_syms, size_t sym_stride_bytes, uint8_t* d_data,
                                       size_t out_stride_bytes, unsigned nbits) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");

@@ -374,7 +374,8 @@ def test_k24_renormalisation_and_streaming():
                 assert np.array_equal(out[f], qo), (chunks, f)
 
 
-@pytest.mark.parametrize("name", ["ka9q27", "spiral29", "ka9q29", "wy_sse_u16_k7r2"])
+@pytest.mark.parametrize("name", ["ka9q27", "spiral27", "spiral47", "wy_sse_u8_k7r4", "wy_sse_u8_k7r3", "spiral29", "ka9q29",
+                                  "wy_sse_u16_k7r2"])
 def test_pipelined_batch_decode_matches_whole_batch_launch(name):
     """b200v_batch_decode cuts large batches into chunks of frames that flow through several streams (copy /
     compute overlap); the result must equal init + update + chainback of the whole batch, and the oracle."""
@@ -397,7 +398,7 @@ def test_pipelined_batch_decode_matches_whole_batch_launch(name):
         dec.update(syms)
         out_whole = dec.chainback(nbits)
         assert np.array_equal(out_pipe, out_whole)
-        # device-pointer entry (chunks over internal streams, ordered on the instance's stream)
+        # device-pointer entry; K=7: chunks of frames, update of chunk k fused with the chainback of chunk k-1
         d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
         dec.decode_dev(d_syms, T * R * sb, d_out, nbytes, nbits)
         dec.sync()
