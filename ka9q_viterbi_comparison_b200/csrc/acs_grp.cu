@@ -50,7 +50,7 @@ struct Cfg {
     static constexpr int THREADS = TPF * FPB;
     static constexpr int MET_STRIDE = S * 2 + (TPF < 32 ? 16 : 0);   // bytes of exchange buffer per frame
     static constexpr bool modular = (POLICY == P_KA9Q_U8_MOD);
-    static constexpr int ESHIFT = modular ? 4 : 3;              // table entry: {W, Wc} or {W, Wc, X0, X1}
+    static constexpr int ESHIFT = 3;                            // table entry: {W, Wc}
     static constexpr int SUBTAB = NCW << ESHIFT;                // one step's table
     static constexpr int TAB_BYTES = 2 * NL * SUBTAB;           // two groups (double buffer) x five steps
     // Several frames per warp (K=9) read their own tables with one LDS: frame f's tables must sit in other banks
@@ -78,6 +78,7 @@ struct Cfg {
     // steps run without the frame-wide minimum and its barrier. Block-uniform only when a frame owns the block.
     static constexpr bool DEFER = (TOP == 65535) && TPF >= 32;
     static_assert(NXB >= 3, "at least 4 threads per frame");
+    static_assert(!modular || TPF < 32, "the modular prologue unwraps around state 0 with a warp shuffle");
     static_assert(TPF <= 4 || NXB + 1 >= 10, "exchange swizzle is written for K=9 and K=15");
 };
 
@@ -91,6 +92,7 @@ struct GrpArgs {
     int frame0, count;             // frames [frame0, frame0 + count) of the n_frames-wide layout
     int C, thr, soft_hi, soft_lo;
     int one;                       // 1 (a multiplier ptxas cannot fold: keeps the lo-path adds on the FMA pipe)
+    int zero;                      // 0 (a third add operand ptxas cannot fold: keeps an add on the ALU pipe as IADD3)
 };
 
 // symbol i of a step (u8 for ka9q/spiral, int8 / int16 for the williamyang policies)
@@ -257,18 +259,17 @@ struct PairLoop {
         constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
         constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
         if constexpr (POLICY == P_KA9Q_U8_MOD) {
-            // ka9q modular policy (viterbi29_sse2.cpp:137-158): lanes hold metric << 8, so 16-bit wrap-around is
-            // the reference's mod-256 arithmetic and the s16 sign of a difference is its (int8) sign.
-            //   t0 = m0 - m1 = (A + ~B) + X0,  X0 = W - Wc + 1;   t1 = m2 - m3 = (A + ~B) + X1,  X1 = Wc - W + 1
-            //   decision = t > 0 (tie -> 0);  survivor = hi path + min(t, 0)
-            uint32_t W, Wc, X0, X1;
-            lds128(A ^ (c << 4), W, Wc, X0, X1);
-            const uint32_t dd = __vadd2(w[iA], ~w[iB]);
-            const uint32_t m1 = __vadd2(w[iB], Wc), m3 = __vadd2(w[iB], W);
-            const uint32_t z0 = relu_neg_facc<KK>(__vadd2(dd, X0), d.al, d.ah);
-            const uint32_t z1 = relu_neg_facc<KK>(__vadd2(dd, X1), d.bl, d.bh);
-            w[iA] = __vadd2(m1, z0);
-            w[iB] = __vadd2(m3, z1);
+            // ka9q modular policy (viterbi29_sse2.cpp:137-158): the lanes hold the UNWRAPPED metric U (reference
+            // metric = U mod 256; the kernel prologue unwraps around state 0). The reference relies on the metric
+            // spread staying below 128, so its (int8)(m0 - m1) > 0 is the plain U compare: survivor = min,
+            // decision = (lo path > hi path), tie -> 0. No saturation, no renormalisation: four plain adds (two on
+            // each pipe), two packed mins, predicated FADD decisions.
+            uint32_t W, Wc;
+            lds64(A ^ (c << 3), W, Wc);
+            const uint32_t m0 = add_fma(w[iA], one, W), m1 = add_alu(w[iB], Wc, clamp);
+            const uint32_t m2 = add_fma(w[iA], one, Wc), m3 = add_alu(w[iB], W, clamp);
+            w[iA] = min_facc_strict<KK>(m0, m1, d.al, d.ah);
+            w[iB] = min_facc_strict<KK>(m2, m3, d.bl, d.bh);
             PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, one, d);
             return;
         }
@@ -398,14 +399,14 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
         }
         // code words of this thread: c = tx * NPT + j; the two top bits of c come from tx
         int top = ((tx & 1) ? v1[LOGN] : v0[LOGN]) + ((tx & 2) ? v1[LOGN + 1] : v0[LOGN + 1]);
-        uint32_t X[NPT];                                // (bm, cm) packed; scaled by 256 for the modular policy
+        uint32_t X[NPT];                                // (bm, cm) packed
 #pragma unroll
         for (int j = 0; j < NPT; j++) {
             int sum = top;
 #pragma unroll
             for (int i = 0; i < LOGN; i++) sum += ((j >> i) & 1) ? v1[i] : v0[i];
             const int bm = bm_post<POLICY>(sum), cm = max(a.C - bm, 0);
-            X[j] = CF::modular ? pack2((uint32_t)bm << 8, (uint32_t)cm << 8) : pack2((uint32_t)bm, (uint32_t)cm);
+            X[j] = pack2((uint32_t)bm, (uint32_t)cm);
         }
         const unsigned fp = CF::PERMUTE ? (((fl & 1) ? frame_perm<CODE>(s, 1) : 0u) ^ ((fl & 2) ? frame_perm<CODE>(s, 2) : 0u)) : 0u;
         const uint32_t st = buf + (uint32_t)s * CF::SUBTAB;
@@ -415,10 +416,6 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
             const int jp = j ^ (int)(D & (NPT - 1));
             const uint32_t Xd = (D >> LOGN) ? __shfl_xor_sync(0xffffffffu, X[jp], (int)(D >> LOGN)) : X[jp];
             const uint32_t W = __byte_perm(X[j], Xd, 0x5410), Wc = __byte_perm(X[j], Xd, 0x7632);
-            if (CF::modular)
-                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(st + (((c0 + j) ^ fp) << 4)), "r"(W), "r"(Wc),
-                             "r"(__vadd2(__vsub2(W, Wc), 0x00010001u)), "r"(__vadd2(__vsub2(Wc, W), 0x00010001u)) : "memory");
-            else
                 sts64(st + (((c0 + j) ^ fp) << 3), W, Wc);
         }
     }
@@ -451,15 +448,7 @@ __device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned cha
         bm_eval<POLICY, R>(c1, sym, a, b1, m1);
         bm_eval<POLICY, R>(c2, sym, a, b2, m2);
         const uint32_t st = buf + (uint32_t)s * CF::SUBTAB;
-        if (CF::modular) {       // scaled by 256; X0 = W - Wc + 1, X1 = Wc - W + 1 per 16-bit lane
-            const uint32_t d2 = D ? b2 : b1, e2 = D ? m2 : m1;     // second lane of entry c1 (entry c2 mirrors it)
-            const uint32_t Wa = pack2(b1 << 8, d2 << 8), Wca = pack2(m1 << 8, e2 << 8);
-            const uint32_t Wb = pack2(b2 << 8, (D ? b1 : b2) << 8), Wcb = pack2(m2 << 8, (D ? m1 : m2) << 8);
-            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(st + c1 * 16), "r"(Wa), "r"(Wca),
-                         "r"(__vadd2(__vsub2(Wa, Wca), 0x00010001u)), "r"(__vadd2(__vsub2(Wca, Wa), 0x00010001u)) : "memory");
-            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(st + c2 * 16), "r"(Wb), "r"(Wcb),
-                         "r"(__vadd2(__vsub2(Wb, Wcb), 0x00010001u)), "r"(__vadd2(__vsub2(Wcb, Wb), 0x00010001u)) : "memory");
-        } else if (D) {
+        if (D) {
             sts64(st + c1 * 8, pack2(b1, b2), pack2(m1, m2));
             sts64(st + c2 * 8, pack2(b2, b1), pack2(m2, m1));
         } else {
@@ -539,12 +528,22 @@ acs_grp_kernel(const GrpArgs a) {
         for (int q = 0; q < NREG; q++) {
             w[q] = g32[q * CF::TPF + tx];
             if (CF::s16) w[q] ^= 0x80008000u;          // s16 -> biased u16
-            if (CF::modular) w[q] = (w[q] << 8) & 0xff00ff00u;
+        }
+    }
+    if (CF::modular) {
+        // unwrap the reference's mod-256 metrics around state 0 (spread < 128): U = 256 + m0 + (int8)(m - m0).
+        // State 0 is lane 0 of register 0 of the frame's thread 0 in the phase-0 layout.
+        const int m0 = (int)(__shfl_sync(0xffffffffu, w[0], (tid & 31) & ~(CF::TPF - 1)) & 0xffu);
+#pragma unroll
+        for (int q = 0; q < NREG; q++) {
+            const int lo = 256 + m0 + (int)(int8_t)((w[q] & 0xffu) - m0);
+            const int hi = 256 + m0 + (int)(int8_t)(((w[q] >> 16) & 0xffu) - m0);
+            w[q] = pack2((uint32_t)lo, (uint32_t)hi);
         }
     }
     FrameState fs;
     fs.base = 0;
-    fs.clamp = 0;
+    fs.clamp = CF::modular ? (uint32_t)a.zero : 0u;     // modular policy: no clamp; the slot carries add_alu's zero
     fs.skip = 0;
     {   // min(w) <= TH + skip * bm_max between rebases; window: that + (K + 1) branch metrics of spread and headroom
         const int bmx = max(bm_cap<POLICY, CF::TOP>(a.C), 1);
@@ -590,6 +589,15 @@ acs_grp_kernel(const GrpArgs a) {
         if (nsub > 3) step<POLICY, CODE, CF, 3, false>(w, fs, a, gt + 3 * CF::SUBTAB, cx8[3], drow + 3 * dstride, live, met_addr, s_red, rpar, tid, tx);
         if (nsub > 4) step<POLICY, CODE, CF, 4, true>(w, fs, a, gt + 4 * CF::SUBTAB, cx8[4], drow + 4 * dstride, live, met_addr, s_red, rpar, tid, tx);
         drow += NL * dstride;
+        if (CF::modular && (g & 511) == 511) {
+            // unwrapped lanes gain at most 15 per step: every 2560 steps bring them down by a multiple of 256
+            // (keeps U mod 256), leaving the minimum in [256, 512)
+            uint32_t gmin, g0;
+            frame_min<CF>(local_min(w), w[0], s_red, rpar, tid, gmin, g0);
+            const uint32_t sub = (gmin & ~255u) >= 256u ? (gmin & ~255u) - 256u : 0u;
+#pragma unroll
+            for (int i = 0; i < NREG; i++) w[i] -= sub * 0x10001u;
+        }
     }
 
     // ---- registers (phase pf layout) -> canonical metrics, through shared memory ----
@@ -607,7 +615,7 @@ acs_grp_kernel(const GrpArgs a) {
             locate_state(CF::NXB, pf, n, q, xx);
             const int rv = (int)raw[(q * CF::TPF + (int)(xx >> 1)) * 2 + (int)(xx & 1u)];
             const int tb = rv + fs.base;
-            gm[n] = (uint16_t)(CF::modular ? (rv >> 8) : CF::s16 ? (tb ^ 0x8000) : tb);
+            gm[n] = (uint16_t)(CF::modular ? (rv & 0xff) : CF::s16 ? (tb ^ 0x8000) : tb);
         }
     }
 }
@@ -693,7 +701,7 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;
-    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1;
+    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1; a.zero = 0;
     switch (grp::find_instance(c)) {
     case grp::I_WY8_IS95: return grp::launch_one<P_WY_U8, grp::CodeIS95>(a, st);
     case grp::I_WY16_IS95: return grp::launch_one<P_WY_U16, grp::CodeIS95>(a, st);

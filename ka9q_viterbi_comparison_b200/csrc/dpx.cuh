@@ -44,6 +44,18 @@ __device__ __forceinline__ uint32_t min_facc(uint32_t a, uint32_t b, float& acc_
         : "=&r"(s), "+f"(acc_lo), "+f"(acc_hi) : "r"(a), "r"(b), "f"((float)(1u << BIT)));
     return s;
 }
+// min(a, b) per u16 lane with the opposite tie-break: decision = (min != a), i.e. b survived strictly (tie -> 0)
+template <int BIT>
+__device__ __forceinline__ uint32_t min_facc_strict(uint32_t a, uint32_t b, float& acc_lo, float& acc_hi) {
+    uint32_t s;
+    asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+        "min.u16x2 %0, %3, %4;\n\t"
+        "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %3;\n\t"
+        "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
+        "@!pv add.rn.f32 %1, %1, %5;\n\t@!pu add.rn.f32 %2, %2, %5;\n\t}"
+        : "=&r"(s), "+f"(acc_lo), "+f"(acc_hi) : "r"(a), "r"(b), "f"((float)(1u << BIT)));
+    return s;
+}
 // z = min(t, 0) per s16 lane; decision of a lane = (t > 0), accumulated like min_facc
 template <int BIT>
 __device__ __forceinline__ uint32_t relu_neg_facc(uint32_t t, float& acc_lo, float& acc_hi) {

@@ -538,3 +538,27 @@ def test_common_codes(code, width):
                 assert np.array_equal(dec.decisions(f, 0, T), qd), f"v{v} frame {f}: decisions"
                 assert np.array_equal(dec.metrics(f), qm), f"v{v} frame {f}: metrics"
                 assert np.array_equal(out[f], qo), f"v{v} frame {f}: decoded bytes"
+
+
+@pytest.mark.parametrize("name", ["ka9q29", "ka9q27"])
+def test_modular_policy_long_update_rebases_the_unwrapped_lanes(name):
+    """The ka9q modular kernels keep unwrapped metrics in 16-bit lanes and bring them down by a multiple of 256
+    every few thousand steps; frames longer than that interval must still match the reference bit for bit."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes, n_frames = 700, 5
+    T = nbytes * 8 + K - 1            # 5608 / 5606 steps: past two rebase points of the K=9 kernel
+    data, syms = make_batch(c, n_frames, nbytes, 0.9, seed=0x10E6)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        assert dec.variant == 2
+        dec.reset()
+        dec.update(syms)
+        out = dec.chainback(nbytes * 8)
+        for f in range(n_frames):
+            q = o.Oracle(c, T)
+            q.init(0)
+            q.update(syms[f], T)
+            assert np.array_equal(dec.decisions(f, 0, T), q.decisions(0, T)), f"frame {f}: decisions"
+            assert np.array_equal(dec.metrics(f), q.metrics()), f"frame {f}: metrics"
+            assert np.array_equal(out[f], q.chainback(nbytes * 8, 0)), f"frame {f}: decoded bytes"
+            q.close()
