@@ -345,7 +345,8 @@ def run_b200_arm(args):
     lane_ops = frames * T * 4.0 * S                      # 4*S integer lane-ops per step
     traffic, traffic_src = None, None
     try:     # DRAM bytes per launch as ncu measured them (profiles/ncu_traffic.json: per frame-step, scaled to this launch)
-        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.codec)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(
+            f"{args.codec}_k{K}r{R}" if args.codec.startswith("wy_") else args.codec)
         if tr:
             traffic, traffic_src = tr["bytes_per_frame_step"] * frames * T, tr["capture"]
     except Exception:
