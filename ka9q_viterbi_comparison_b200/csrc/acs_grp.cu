@@ -77,6 +77,12 @@ struct Cfg {
     // the next `skip` steps provably cannot trigger (state 0 gains at most one branch metric per step), so those
     // steps run without the frame-wide minimum and its barrier. Block-uniform only when a frame owns the block.
     static constexpr bool DEFER = (TOP == 65535) && TPF >= 32;
+    // 8-bit policies trigger every few steps, but the trigger itself needs only state 0's metric: a frame that owns
+    // its block broadcasts that one lane per step and reduces the frame-wide minimum only on the steps that
+    // renormalise (block-uniform branch). Lanes cannot overflow in between: w = tb - base <= 255 - base.
+    // Measured, K=15 at sigma = 1: wy-u8 (threshold 183, triggers every ~20 steps) 43.9 -> 39.0 ms per 8192 frames;
+    // spiral615 (threshold 74, triggers every few steps, two barriers on those) 43.5 -> 46.1 ms: stays eager.
+    static constexpr bool LAZY = (POLICY == P_WY_U8) && TPF >= 32;
     static_assert(NXB >= 3, "at least 4 threads per frame");
     static_assert(!modular || TPF < 32, "the modular prologue unwraps around state 0 with a warp shuffle");
     static_assert(TPF <= 4 || NXB + 1 >= 10, "exchange swizzle is written for K=9 and K=15");
@@ -486,6 +492,22 @@ __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const 
             }
             return;
         }
+    }
+    if constexpr (CF::LAZY) {
+        uint32_t* r = s_red + rpar * 16;
+        if (tid == 0) r[15] = w[0] & 0xffffu;           // state 0: lane 0 of register 0 of thread 0 in every phase
+        if (EXCH) exchange_store<CF>(w, met_addr, tx);
+        __syncthreads();
+        const uint32_t g0 = r[15];
+        rpar ^= 1;
+        if (EXCH) exchange_load<CF>(w, met_addr, tx);
+        const int tb0 = (int)g0 + fs.base;
+        if (CF::strict ? (tb0 > a.thr) : (tb0 >= a.thr)) {      // uniform over the block
+            uint32_t gmin, g0b;
+            frame_min<CF>(local_min(w), 0u, s_red, rpar, tid, gmin, g0b);
+            renorm<POLICY, CF>(w, fs, gmin, g0, a);
+        }
+        return;
     }
     const uint32_t lm = local_min(w);
     const uint32_t w0 = w[0];
