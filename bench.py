@@ -24,6 +24,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "decoded Mbit/s (update+chainback)"
 UNIT = "Mbit/s"
+ALU_PEAK = 148 * 128 * 1.965e9      # dual-pipe integer issue peak, thread-instructions/s (measured 96-121 of 128 lanes)
 
 
 def parse():
@@ -354,7 +355,11 @@ def run_b200_arm(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
                 "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": frames * T * bytes_per_step_frame, "kernel": "update", "kernel_ms": upd, "chainback_ms": cb,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
-                "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "note": "4*S integer lane-ops per trellis step"}}
+                # the roofline that actually binds the update kernels: integer issue, two pipes of 64 lanes
+                # per clock and SM at the measured SM clock limit (tools/ubench_int.cu, profiles/r01_ubench_int_pipes.jsonl)
+                "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "peak_lane_ops_per_s": ALU_PEAK,
+                        "frac": lane_ops / (upd * 1e-3) / ALU_PEAK,
+                        "note": "4*S integer lane-ops per trellis step (SURVEY 8d) vs 148 SMs x 128 lanes/clk x 1.965 GHz"}}
 
     cpu = None
     if not args.no_cpu_baseline:

@@ -182,6 +182,11 @@ static int popcount32(uint32_t x) { return __builtin_popcount(x); }
 
 static int create_impl(b200v_batch* h, int starting_state);
 
+// automatic kernel family: the specialised one where it exists; otherwise warp-per-frame for K=7 (any polynomial
+// set, ~4x the generic kernel), else the generic shared-memory kernel. Families 1 and 3 share the decision layout.
+static int fallback_variant(const b200v_batch* h) { return h->has_fast ? 2 : k7_warp_supported(h->c) ? 3 : 1; }
+static int exact_variant(const b200v_batch* h) { return k7_warp_supported(h->c) ? 3 : 1; }
+
 extern "C" b200v_batch* b200v_batch_create(int codec, int K, int R, const int* poly, int frame_steps,
                                            int n_frames, int device, const b200v_wy_config* wy_config) {
     CodecParams c;
@@ -253,7 +258,7 @@ static int create_impl(b200v_batch* h, int starting_state) {
     // use 8 bytes per (row, frame) for K=7, so they share the decision buffer
     h->fast_layout = k7_supported(c) ? DL_K7_INTERLEAVED : grp_supported(c) ? DL_GRP_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
     h->has_fast = h->fast_layout != DL_BALLOT_FRAME_MAJOR;
-    h->variant = h->has_fast ? 2 : 1;
+    h->variant = fallback_variant(h);
     h->layout = h->fast_layout;
     return b200v_batch_init(h, starting_state);
 }
@@ -267,7 +272,7 @@ extern "C" int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream) {
 extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     h->user_variant = variant != 0;
-    if (variant == 0) variant = h->has_fast ? 2 : 1;
+    if (variant == 0) variant = fallback_variant(h);
     if (variant != h->variant && h->cursor != 0)
         return fail(B200V_ERR_STATE, "the kernel family can only change right after init (decision layouts differ)");
     if (variant == 1 && h->generic_ok) { h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR; return B200V_OK; }
@@ -285,7 +290,7 @@ extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     h->cursor = 0;
     h->cur_metrics = 0;
     if (!h->user_variant && h->layout != DL_CANONICAL) {     // back to the automatic family (wy-u16 may have left it)
-        h->variant = h->has_fast ? 2 : 1;
+        h->variant = fallback_variant(h);
         h->layout = h->has_fast ? h->fast_layout : DL_BALLOT_FRAME_MAJOR;
     }
     return B200V_OK;
@@ -383,7 +388,7 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
                 return fail(B200V_ERR_ARG, "int16 symbols beyond +-%d in a continued update: the specialised u16 kernels "
                             "cannot take over mid-frame; select the generic family (variant 1) after init",
                             wy16_symbol_limit(c));
-            h->variant = 1; h->layout = DL_BALLOT_FRAME_MAJOR;      // exact for any input
+            h->variant = exact_variant(h); h->layout = DL_BALLOT_FRAME_MAJOR;      // exact for any input
         }
     }
     CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
