@@ -155,6 +155,7 @@ struct b200v_batch {
     int* d_results = nullptr;
     unsigned* d_best = nullptr;  // per-frame best end states (b200v_batch_chainback_best_dev)
     int* d_scan = nullptr;       // wy-u16 symbol range check
+    K24GraphCache k24_graph;     // K=24: captured step loop of the last update call
     bool user_variant = false;   // set_variant() was called: no automatic family changes
     // lazily allocated staging for the host-pointer entry points
     void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
@@ -165,6 +166,7 @@ static void free_all(b200v_batch* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+    k24_graph_cache_release(&h->k24_graph);
     cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase); cudaFree(h->d_scan); cudaFree(h->d_best);
     cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
@@ -345,7 +347,7 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
         if (f0 != 0 || cnt != h->n_frames) return fail(B200V_ERR_STATE, "the K=24 family works on whole batches");
         CUDA_TRY(launch_acs_k24(c, d_syms, stride, nsteps, step0, (uint32_t*)h->d_dec, h->dec_rows,
                                 h->d_metrics, h->d_metrics2, &h->cur_metrics, h->d_gmin, h->d_adj, h->n_frames,
-                                &h->launches, st));
+                                &h->launches, &h->k24_graph, st));
     } else if (h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
         CUDA_TRY(launch_acs_grp(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
                                 h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));

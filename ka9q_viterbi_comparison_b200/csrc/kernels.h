@@ -47,9 +47,19 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
                            int frame0, int count, cudaStream_t st);
 
 // ---- K=24 (acs_k24.cu): one launch per trellis step, ping-pong metric buffers, canonical decision rows ----
+// replay cache of the captured step loop of one update call (acs_k24.cu)
+struct K24GraphCache {
+    void* exec = nullptr;            // cudaGraphExec_t
+    const void* syms = nullptr; size_t sym_stride = 0;
+    int nsteps = 0, step0 = 0, cur = 0, n_frames = 0, cur_after = 0;
+    long long kernels = 0;
+    cudaStream_t stream = nullptr;
+};
 cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
-                           int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st);
+                           int* gmin, int* adj, int n_frames, long long* launches, K24GraphCache* cache,
+                           cudaStream_t st);
+void k24_graph_cache_release(K24GraphCache* cache);
 
 // ---- chainback (chainback.cu) ---------------------------------------------------------------------
 struct ChainbackArgs {
