@@ -258,7 +258,8 @@ static int create_impl(b200v_batch* h, int starting_state) {
     CUDA_TRY(cudaMemsetAsync(h->d_row_phase, 0, (size_t)h->dec_rows, h->stream));
     // the register-resident family exists for the polynomial sets it was instantiated for; both families
     // use 8 bytes per (row, frame) for K=7, so they share the decision buffer
-    h->fast_layout = k7_supported(c) ? DL_K7_INTERLEAVED : grp_supported(c) ? DL_GRP_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
+    h->fast_layout = k7_supported(c) ? DL_K7_INTERLEAVED : grp_supported(c) ? DL_GRP_INTERLEAVED :
+                     smallk_supported(c) ? DL_SMALLK_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
     h->has_fast = h->fast_layout != DL_BALLOT_FRAME_MAJOR;
     h->variant = fallback_variant(h);
     h->layout = h->fast_layout;
@@ -352,6 +353,13 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
         CUDA_TRY(launch_acs_grp(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
                                 h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
         h->launches++;
+    } else if (h->variant == 2 && h->layout == DL_SMALLK_INTERLEAVED) {
+        GenericArgs a{};
+        a.c = c; a.syms = d_syms; a.sym_stride = stride; a.nsteps = nsteps; a.step0 = step0;
+        a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = 1;
+        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
+        CUDA_TRY(launch_acs_smallk(a, st));
+        h->launches++;
     } else if (h->variant == 2) {
         CUDA_TRY(launch_acs_k7(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
                                h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
@@ -382,7 +390,7 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
     if (nsteps > 0 && frame_stride_bytes < (size_t)nsteps * c.R * c.sym_bytes && h->n_frames > 1)
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
-    if (c.policy == P_WY_U16 && h->variant == 2 && nsteps > 0) {
+    if (c.policy == P_WY_U16 && h->variant == 2 && h->layout != DL_SMALLK_INTERLEAVED && nsteps > 0) {   // small-K: exact for any input
         const int ok = wy16_symbols_in_range(h, d_syms, frame_stride_bytes, nsteps);
         if (ok < 0) return ok;
         if (!ok) {
@@ -623,6 +631,17 @@ extern "C" int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, i
                 o[n >> 3] |= (uint8_t)(((r[w] >> b) & 1u) << (n & 7));
             }
         }
+        return B200V_OK;
+    }
+    if (h->layout == DL_SMALLK_INTERLEAVED) {
+        std::vector<uint32_t> rows((size_t)nsteps);
+        const uint32_t* src = (const uint32_t*)h->d_dec + (size_t)step0 * h->n_frames + frame;
+        if (nsteps > 0) {
+            CUDA_TRY(cudaMemcpy2DAsync(rows.data(), sizeof(uint32_t), src, (size_t)h->n_frames * sizeof(uint32_t),
+                                       sizeof(uint32_t), (size_t)nsteps, cudaMemcpyDeviceToHost, h->stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        }
+        for (int t = 0; t < nsteps; t++) memcpy(out + (size_t)t * nb, &rows[t], nb);    // little-endian bit n = state n
         return B200V_OK;
     }
     if (h->layout == DL_K7_INTERLEAVED) {

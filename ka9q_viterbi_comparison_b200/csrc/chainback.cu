@@ -134,6 +134,7 @@ cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
     case DL_K7_INTERLEAVED: chainback_k7_kernel<<<blocks, threads, 0, st>>>(a); break;
     case DL_GRP_INTERLEAVED: chainback_kernel<DL_GRP_INTERLEAVED><<<blocks, threads, 0, st>>>(a); break;
     case DL_CANONICAL: chainback_kernel<DL_CANONICAL><<<blocks, threads, 0, st>>>(a); break;
+    case DL_SMALLK_INTERLEAVED: chainback_kernel<DL_SMALLK_INTERLEAVED><<<blocks, threads, 0, st>>>(a); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -45,6 +45,9 @@ enum DecisionLayout : int {
     DL_GRP_INTERLEAVED = 2,
     // K=24 family (acs_k24.cu): the canonical vector itself, frame-major: bit n of dec[frame][step][S/32 words]
     DL_CANONICAL = 3,
+    // small-K register kernel (acs_smallk.cu, K <= 6): the canonical vector in one u32 per (step, frame),
+    // frame-interleaved: bit n of dec[step][frame]
+    DL_SMALLK_INTERLEAVED = 4,
 };
 
 static inline bool policy_is_spiral(int p) { return p == P_SPIRAL_R2 || p == P_SPIRAL_R4 || p == P_SPIRAL_615; }

@@ -47,6 +47,16 @@ template <> struct DecisionReader<DL_K7_INTERLEAVED> {
     }
 };
 
+template <> struct DecisionReader<DL_SMALLK_INTERLEAVED> {
+    const uint32_t* base;             // + frame
+    size_t stride;                    // n_frames
+    __device__ DecisionReader(const ChainbackArgs& a, int frame)
+        : base((const uint32_t*)a.dec + frame), stride((size_t)a.n_frames) {}
+    __device__ __forceinline__ unsigned bit(unsigned row, unsigned state) const {
+        return (__ldg(base + (size_t)row * stride) >> state) & 1u;
+    }
+};
+
 template <> struct DecisionReader<DL_CANONICAL> {
     const uint32_t* base;
     int row_words;

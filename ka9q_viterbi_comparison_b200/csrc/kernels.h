@@ -25,6 +25,10 @@ struct GenericPlan { int threads_per_frame, frames_per_block, smem_bytes; };
 GenericPlan generic_plan(const CodecParams& c);
 cudaError_t launch_acs_generic(const GenericArgs& a, cudaStream_t st);
 
+// ---- K = 3 ... 6 register kernel (acs_smallk.cu): thread per frame, u32 decision word per (row, frame) ----
+bool smallk_supported(const CodecParams& c);
+cudaError_t launch_acs_smallk(const GenericArgs& a, cudaStream_t st);
+
 // ---- K=7 warp-per-frame kernel (acs_k7_warp.cu): the alternative design, kept for the measured comparison ----
 bool k7_warp_supported(const CodecParams& c);
 cudaError_t launch_acs_k7_warp(const GenericArgs& a, cudaStream_t st);

@@ -513,7 +513,7 @@ def test_best_state_traceback_of_unterminated_streams(name):
 @pytest.mark.parametrize("width", [8, 16])
 def test_common_codes(code, width):
     """Every entry of the williamyang library's code list (examples/helpers/common_codes.h:23-30), both metric
-    widths, every kernel family the instance offers; K >= 7 entries must be served by a specialised family."""
+    widths, every kernel family the instance offers; all of them must be served by a specialised family."""
     _, K, R, poly = code
     c = o.codec_wy(width, K, R, poly)
     nbytes = 16 if K == 15 else 96
@@ -528,7 +528,7 @@ def test_common_codes(code, width):
         refs.append((q.decisions(0, T), q.metrics(), q.chainback(nbytes * 8, 0)))
         q.close()
     with kv.BatchDecoder(kv.WY_U8 if width == 8 else kv.WY_U16, T, n_frames, K=K, R=R, poly=poly) as dec:
-        assert dec.variant == (2 if K >= 7 else 1), "kernel family chosen for this code"
+        assert dec.variant == 2, "every common code has a specialised kernel family"
         for v in variants(dec):
             dec.reset()
             dec.set_variant(v)
