@@ -24,55 +24,92 @@ constexpr int K24_BPT = 8;           // butterflies per thread: 16 B + 16 B in, 
 constexpr int K24_THREADS = 256;
 
 struct K24Args {
-    const uint16_t* old_m;          // [n_frames][S] raw s16 bit patterns
+    const uint16_t* old_m;          // [n_frames][S] raw 16-bit patterns (s16 for ka9q224, u16 / u8 values for wy)
     uint16_t* new_m;
-    const unsigned char* syms; size_t sym_stride;   // symbols of THIS step start at syms + step*2
+    const unsigned char* syms; size_t sym_stride;   // symbols of THIS step start at syms + step*2*sym_bytes
     int step;                        // step index inside this update call
     uint16_t* dec;                   // canonical row of this step: dec + frame * dec_frame_stride (u16 units)
     size_t dec_frame_stride;
-    int* gmin_prev;                  // [n_frames] minimum (s16 value) of old_m, or nullptr when nothing is pending
+    int* gmin_prev;                  // [n_frames] minimum of old_m, or nullptr when nothing is pending
     int* gmin_cur;                   // [n_frames] slot this step reduces into (pre-set to INT_MAX)
     unsigned poly0, poly1;
     int S, thr;
+    int C, soft_hi, soft_lo;         // williamyang policies: max_error and the two soft-decision levels
 };
 
-// pending renormalisation of the buffer a launch reads: adj = min - SHRT_MIN if old[0] >= thr, else 0
-__device__ __forceinline__ int pending_adjust(const uint16_t* old_frame, const int* gmin_prev, int frame, int thr) {
-    if (!gmin_prev) return 0;
-    const int m0 = (int)(int16_t)old_frame[0];
-    return m0 >= thr ? gmin_prev[frame] + 32768 : 0;
+// metric as an integer: signed for the ka9q s16 policy, unsigned for the williamyang policies
+template <int POLICY> __device__ __forceinline__ int k24_value(unsigned raw16) {
+    return POLICY == P_KA9Q_S16_224 ? (int)(int16_t)(uint16_t)raw16 : (int)(raw16 & 0xffffu);
 }
 
+// pending renormalisation of the buffer a launch reads, as the amount to subtract (mod 2^16) from every metric:
+// ka9q224: min - SHRT_MIN if old[0] >= thr (viterbi224_sse2.cpp:226-246); williamyang: min if old[0] >= thr
+// (sse_u8.h:63-65,127-154, sse_u16.h:152-177)
+template <int POLICY>
+__device__ __forceinline__ int pending_adjust(const uint16_t* old_frame, const int* gmin_prev, int frame, int thr) {
+    if (!gmin_prev) return 0;
+    const int m0 = k24_value<POLICY>(old_frame[0]);
+    if (m0 < thr) return 0;
+    return POLICY == P_KA9Q_S16_224 ? gmin_prev[frame] + 32768 : gmin_prev[frame];
+}
+
+template <int POLICY>
 __global__ void __launch_bounds__(K24_THREADS) acs_k24_kernel(const K24Args a) {
+    constexpr bool WY = (POLICY != P_KA9Q_S16_224);
+    constexpr int TOP = POLICY == P_WY_U8 ? 255 : POLICY == P_WY_U16 ? 65535 : 32767;
     const int frame = blockIdx.y;
     const int H = a.S >> 1;
     const int j0 = (blockIdx.x * K24_THREADS + threadIdx.x) * K24_BPT;     // first butterfly of this thread
     const uint16_t* old_f = a.old_m + (size_t)frame * a.S;
     uint16_t* new_f = a.new_m + (size_t)frame * a.S;
-    const int adj = pending_adjust(old_f, a.gmin_prev, frame, a.thr);
+    const int adj = pending_adjust<POLICY>(old_f, a.gmin_prev, frame, a.thr);
 
-    const unsigned char* sp = a.syms + (size_t)frame * a.sym_stride + (size_t)a.step * 2;
-    const int s0 = sp[0], s1 = sp[1];
+    int s0, s1;
+    int e00 = 0, e01 = 0, e10 = 0, e11 = 0;          // williamyang: |sat(bt - s_i)| for bt = lo / hi, symbol i
+    if (POLICY == P_WY_U16) {
+        const int16_t* sp = reinterpret_cast<const int16_t*>(a.syms + (size_t)frame * a.sym_stride) + (size_t)a.step * 2;
+        s0 = sp[0]; s1 = sp[1];
+        e00 = abs(clamp_i(a.soft_lo - s0, -32768, 32767)); e01 = abs(clamp_i(a.soft_hi - s0, -32768, 32767));
+        e10 = abs(clamp_i(a.soft_lo - s1, -32768, 32767)); e11 = abs(clamp_i(a.soft_hi - s1, -32768, 32767));
+    } else if (POLICY == P_WY_U8) {
+        const int8_t* sp = reinterpret_cast<const int8_t*>(a.syms + (size_t)frame * a.sym_stride) + (size_t)a.step * 2;
+        s0 = sp[0]; s1 = sp[1];
+        e00 = abs(clamp_i(a.soft_lo - s0, -128, 127)); e01 = abs(clamp_i(a.soft_hi - s0, -128, 127));
+        e10 = abs(clamp_i(a.soft_lo - s1, -128, 127)); e11 = abs(clamp_i(a.soft_hi - s1, -128, 127));
+    } else {
+        const unsigned char* sp = a.syms + (size_t)frame * a.sym_stride + (size_t)a.step * 2;
+        s0 = sp[0]; s1 = sp[1];
+    }
 
     const uint4 lo4 = *reinterpret_cast<const uint4*>(old_f + j0);
     const uint4 hi4 = *reinterpret_cast<const uint4*>(old_f + H + j0);
     const uint32_t lw[4] = { lo4.x, lo4.y, lo4.z, lo4.w }, hw[4] = { hi4.x, hi4.y, hi4.z, hi4.w };
     uint32_t out[8];
     unsigned dbits = 0;
-    int mn = 32767;
+    int mn = TOP;
 #pragma unroll
     for (int k = 0; k < K24_BPT; k++) {
         const int j = j0 + k;
-        // wrapping 16-bit subtract of the pending adjustment (viterbi224_sse2.cpp:243-244)
-        const int lo = (int)(int16_t)(uint16_t)(((lw[k >> 1] >> ((k & 1) * 16)) & 0xffffu) - (unsigned)adj);
-        const int hi = (int)(int16_t)(uint16_t)(((hw[k >> 1] >> ((k & 1) * 16)) & 0xffffu) - (unsigned)adj);
-        const int x0 = (__popc((2u * (unsigned)j) & a.poly0) & 1) ? (s0 ^ 255) : s0;
-        const int x1 = (__popc((2u * (unsigned)j) & a.poly1) & 1) ? (s1 ^ 255) : s1;
-        const int bm = x0 + x1, cm = 510 - bm;
-        const int m0 = min(lo + bm, 32767), m1 = min(hi + cm, 32767);
-        const int m2 = min(lo + cm, 32767), m3 = min(hi + bm, 32767);
-        const int d0 = m0 > m1, d1 = m2 > m3;
-        const int v0 = min(m0, m1), v1 = min(m2, m3);
+        // wrapping 16-bit subtract of the pending adjustment (viterbi224_sse2.cpp:243-244; the williamyang
+        // subtract cannot go below zero: every metric >= the minimum)
+        const int lo = k24_value<POLICY>(((lw[k >> 1] >> ((k & 1) * 16)) & 0xffffu) - (unsigned)adj);
+        const int hi = k24_value<POLICY>(((hw[k >> 1] >> ((k & 1) * 16)) & 0xffffu) - (unsigned)adj);
+        const bool b0 = __popc((2u * (unsigned)j) & a.poly0) & 1, b1 = __popc((2u * (unsigned)j) & a.poly1) & 1;
+        int bm, cm, d0, d1, v0, v1;
+        if (WY) {       // sse_u8.h:92-114: saturating error sum, complement = subs(C, BM), tie -> 1
+            bm = min((b0 ? e01 : e00) + (b1 ? e11 : e10), TOP);
+            cm = max(a.C - bm, 0);
+            const int m0 = min(lo + bm, TOP), m1 = min(hi + cm, TOP), m2 = min(lo + cm, TOP), m3 = min(hi + bm, TOP);
+            v0 = min(m0, m1); v1 = min(m2, m3);
+            d0 = (v0 == m1); d1 = (v1 == m3);
+        } else {        // viterbi224_sse2.cpp:159-194: tie -> 0
+            bm = (b0 ? (s0 ^ 255) : s0) + (b1 ? (s1 ^ 255) : s1);
+            cm = 510 - bm;
+            const int m0 = min(lo + bm, 32767), m1 = min(hi + cm, 32767);
+            const int m2 = min(lo + cm, 32767), m3 = min(hi + bm, 32767);
+            d0 = m0 > m1; d1 = m2 > m3;
+            v0 = min(m0, m1); v1 = min(m2, m3);
+        }
         out[k] = (uint32_t)(v0 & 0xffff) | ((uint32_t)(v1 & 0xffff) << 16);
         dbits |= (unsigned)(d0 | (d1 << 1)) << (2 * k);
         mn = min(mn, min(v0, v1));
@@ -97,9 +134,10 @@ __global__ void __launch_bounds__(K24_THREADS) acs_k24_kernel(const K24Args a) {
 
 // apply a pending renormalisation in place (after the last step of an update call). Each frame's trigger is
 // evaluated from a snapshot taken BEFORE any element is modified (snapshot_k24_kernel), so blocks do not race.
+template <int POLICY>
 __global__ void snapshot_k24_kernel(const uint16_t* m, const int* gmin_prev, int* adj_out, int S, int thr, int n_frames) {
     const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < n_frames) adj_out[f] = pending_adjust(m + (size_t)f * S, gmin_prev, f, thr);
+    if (f < n_frames) adj_out[f] = pending_adjust<POLICY>(m + (size_t)f * S, gmin_prev, f, thr);
 }
 __global__ void renorm_k24_kernel(uint16_t* m, const int* adj_in, int S) {
     const int frame = blockIdx.y;
@@ -123,7 +161,8 @@ __global__ void fill_int_kernel(int* p, int n, int v) {
 // Enqueues the launches of `nsteps` steps on `st`. metrics[0] / metrics[1] are the two ping-pong buffers, *cur says
 // which one holds the current metrics (updated on return). gmin: [dec_rows + 1][n_frames] ints of scratch,
 // adj: [n_frames] ints.
-static cudaError_t enqueue_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+template <int POLICY>
+static cudaError_t enqueue_k24_policy(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                                uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
                                int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st) {
     const int S = c.S;
@@ -143,16 +182,39 @@ static cudaError_t enqueue_k24(const CodecParams& c, const void* syms, size_t sy
         a.gmin_cur = gmin + (size_t)t * n_frames;
         a.poly0 = (unsigned)c.poly[0]; a.poly1 = (unsigned)c.poly[1];
         a.S = S; a.thr = c.renorm_threshold;
-        acs_k24_kernel<<<grid, K24_THREADS, 0, st>>>(a);
+        a.C = c.max_error; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
+        acs_k24_kernel<POLICY><<<grid, K24_THREADS, 0, st>>>(a);
         (*launches)++;
         *cur ^= 1;
     }
     // pending renormalisation of the last step
-    snapshot_k24_kernel<<<(n_frames + 127) / 128, 128, 0, st>>>(bufs[*cur], gmin + (size_t)(nsteps - 1) * n_frames, adj,
+    snapshot_k24_kernel<POLICY><<<(n_frames + 127) / 128, 128, 0, st>>>(bufs[*cur], gmin + (size_t)(nsteps - 1) * n_frames, adj,
                                                                  S, c.renorm_threshold, n_frames);
     renorm_k24_kernel<<<dim3(148 * 4, (unsigned)n_frames), 256, 0, st>>>(bufs[*cur], adj, S);
     (*launches) += 2;
     return cudaGetLastError();
+}
+
+static cudaError_t enqueue_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                               uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
+                               int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st) {
+    switch (c.policy) {
+    case P_KA9Q_S16_224:
+        return enqueue_k24_policy<P_KA9Q_S16_224>(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1,
+                                                  cur, gmin, adj, n_frames, launches, st);
+    case P_WY_U8:
+        return enqueue_k24_policy<P_WY_U8>(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur,
+                                           gmin, adj, n_frames, launches, st);
+    case P_WY_U16:
+        return enqueue_k24_policy<P_WY_U16>(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur,
+                                            gmin, adj, n_frames, launches, st);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+bool k24_supported(const CodecParams& c) {
+    return c.K > 16 && c.K <= 24 && c.R == 2 &&
+           (c.policy == P_KA9Q_S16_224 || c.policy == P_WY_U8 || c.policy == P_WY_U16);
 }
 
 // The step loop is launch-bound for small batches (one frame: ~7 us of L2/HBM traffic per launch, ~3.5 us of launch

@@ -197,8 +197,9 @@ extern "C" b200v_batch* b200v_batch_create(int codec, int K, int R, const int* p
         fail(B200V_ERR_ARG, "frame_steps=%d n_frames=%d must be positive", frame_steps, n_frames);
         return nullptr;
     }
-    if (c.K > 16 && c.policy != P_KA9Q_S16_224) {
-        fail(B200V_ERR_ARG, "K=%d: constraint lengths above 16 exist only for the ka9q viterbi224 policy", c.K);
+    if (c.K > 16 && !k24_supported(c)) {
+        fail(B200V_ERR_ARG, "K=%d r=1/%d: constraint lengths above 16 exist for r=1/2 with the ka9q viterbi224 and the "
+             "williamyang policies", c.K, c.R);
         return nullptr;
     }
     b200v_batch* h = new (std::nothrow) b200v_batch();
@@ -390,7 +391,8 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
     if (nsteps > 0 && frame_stride_bytes < (size_t)nsteps * c.R * c.sym_bytes && h->n_frames > 1)
         return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's symbols", frame_stride_bytes);
     CUDA_TRY(cudaSetDevice(h->device));
-    if (c.policy == P_WY_U16 && h->variant == 2 && h->layout != DL_SMALLK_INTERLEAVED && nsteps > 0) {   // small-K: exact for any input
+    if (c.policy == P_WY_U16 && h->variant == 2 && h->layout != DL_SMALLK_INTERLEAVED && h->layout != DL_CANONICAL &&
+        nsteps > 0) {   // the small-K and K=24 kernels compute in int32: exact for any input
         const int ok = wy16_symbols_in_range(h, d_syms, frame_stride_bytes, nsteps);
         if (ok < 0) return ok;
         if (!ok) {

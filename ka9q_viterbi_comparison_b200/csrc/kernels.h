@@ -64,6 +64,7 @@ cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_st
                            int* gmin, int* adj, int n_frames, long long* launches, K24GraphCache* cache,
                            cudaStream_t st);
 void k24_graph_cache_release(K24GraphCache* cache);
+bool k24_supported(const CodecParams& c);       // K = 17 ... 24, r = 1/2: ka9q viterbi224 and the williamyang policies
 
 // ---- chainback (chainback.cu) ---------------------------------------------------------------------
 struct ChainbackArgs {

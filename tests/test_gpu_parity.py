@@ -26,6 +26,7 @@ CASES = {
     "wy_sse_u8_k9r2": (kv.WY_U8, 9, 2), "wy_sse_u16_k9r2": (kv.WY_U16, 9, 2),
     "wy_sse_u8_k9r4": (kv.WY_U8, 9, 4), "wy_sse_u16_k9r4": (kv.WY_U16, 9, 4),
     "wy_sse_u8_k15r6": (kv.WY_U8, 15, 6), "wy_sse_u16_k15r6": (kv.WY_U16, 15, 6),
+    "wy_sse_u8_k24r2": (kv.WY_U8, 24, 2), "wy_sse_u16_k24r2": (kv.WY_U16, 24, 2),     # src/main.cpp:415
 }
 
 
