@@ -101,6 +101,12 @@ int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream);
  * Returns B200V_ERR_ARG if the requested family does not exist for this instance. */
 int b200v_batch_set_variant(b200v_batch* h, int variant);
 int b200v_batch_get_variant(const b200v_batch* h);
+/* Traceback kernel selection. mode 0 = automatic (block-parallel speculative traceback for small and medium
+ * batches, one thread per frame for large ones), 1 = always one thread per frame, 2 = block-parallel whenever
+ * the frame shape allows it (nbits a multiple of 8). warmup_rows = decision rows a block walks before its own
+ * bits to merge with the survivor path (0 = default, max(64, 12*(K-1))); every block boundary is verified and a
+ * mismatch is re-traced sequentially, so the output is bit-exact for ANY warm-up (a short one only costs time). */
+int b200v_batch_set_traceback(b200v_batch* h, int mode, int warmup_rows);
 
 /* init_viterbiXX_sse2(p, starting_state) (viterbi27_sse2.cpp:42-54), init_spiralXX (spiral27.cpp:53-59),
  * ViterbiDecoder_Core::reset (viterbi_decoder_core.h:202-211): all frames. Asynchronous on the stream. */

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libb200viterbi.so")
 COMPAT_SRC = os.path.join(CSRC, "ref_compat.cpp")
 COMPAT_LIB_PATH = os.path.join(PKG_DIR, "libb200viterbi_compat.so")
 INCLUDE_DIR = os.path.join(os.path.dirname(PKG_DIR), "include")
+OBJ_DIR = os.path.join(PKG_DIR, "build")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -54,15 +55,31 @@ def build_library(force=False, verbose=False):
     nvcc = nvcc_path()
     if nvcc is None:
         raise RuntimeError("nvcc not found: cannot build libb200viterbi.so")
-    cmd = [nvcc] + NVCC_FLAGS + ["-I", INCLUDE_DIR, "-o", LIB_PATH] + sources()
-    if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
-    res = subprocess.run(cmd, capture_output=True, text=True)
+    # one object per source, compiled in parallel and reused while it is newer than every header and its source
+    from concurrent.futures import ThreadPoolExecutor
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    hdr_time = max([os.path.getmtime(p) for p in _deps() if p.endswith((".cuh", ".h", ".hpp"))] +
+                   [os.path.getmtime(os.path.abspath(__file__))])
+    compile_flags = [f for f in NVCC_FLAGS if f != "-shared"]
+
+    def compile_one(src):
+        obj = os.path.join(OBJ_DIR, os.path.basename(src) + ".o")
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(hdr_time, os.path.getmtime(src)):
+            return obj, None
+        cmd = [nvcc] + compile_flags + (["-Xptxas", "-v"] if verbose else []) + ["-I", INCLUDE_DIR, "-c", "-o", obj, src]
+        return obj, subprocess.run(cmd, capture_output=True, text=True)
+
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as pool:
+        results = list(pool.map(compile_one, sources()))
+    for obj, res in results:
+        if res is not None and res.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+        if res is not None and verbose:
+            print(res.stderr)
+    res = subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] +
+                         [obj for obj, _ in results], capture_output=True, text=True)
     if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    if verbose:
-        print(res.stderr)
+        raise RuntimeError("nvcc link failed:\n" + res.stdout + res.stderr)
     cxx = shutil.which("g++") or "g++"
     res = subprocess.run([cxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-I", INCLUDE_DIR, "-o", COMPAT_LIB_PATH,
                           COMPAT_SRC, "-L", PKG_DIR, "-lb200viterbi", "-Wl,-rpath,$ORIGIN"],

@@ -20,44 +20,112 @@ namespace b200v {
 
 namespace {
 
-template <int POLICY>
+// policy.cuh's branch_metric with the loop over the R symbols unrolled (RT > 0: compile-time rate), so that the
+// symbols stay in registers
+template <int POLICY, int RT>
+__device__ __forceinline__ int branch_metric_rt(const CodecParams& c, unsigned cw, const int* sym) {
+    constexpr int RMAX = RT ? RT : MAX_R;
+    const int R = RT ? RT : c.R;
+    if (POLICY == P_WY_U8 || POLICY == P_WY_U16) {
+        int tot = 0;
+#pragma unroll
+        for (int i = 0; i < RMAX; i++) {
+            if (i < R) {
+                const int bt = ((cw >> i) & 1u) ? c.soft_hi : c.soft_lo;
+                int e = bt - sym[i];
+                if (POLICY == P_WY_U8) { e = clamp_i(e, -128, 127); e = abs(e); tot = min(tot + e, 255); }
+                else { e = clamp_i(e, -32768, 32767); e = abs(e); tot = min(tot + e, 65535); }
+            }
+        }
+        return tot;
+    }
+    if (POLICY == P_KA9Q_U8_MOD || POLICY == P_SPIRAL_R2) return branch_metric<POLICY>(c, cw, sym);
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < RMAX; i++) {
+        if (i < R) {
+            const int x = ((cw >> i) & 1u) ? (sym[i] ^ 255) : sym[i];
+            s = min(s + ((x >> 2) & 63), 255);
+        }
+    }
+    return (s >> 2) & 63;
+}
+
+// RT = code rate known at compile time (2, 3, 4) or 0: run-time c.R (up to MAX_R).
+// Latency matters here as much as throughput -- this is the family a single frame through the reference's
+// create/init/update/chainback API runs on (src/main.cpp:264-278) -- so nothing in the step loop waits on global
+// memory: the symbols of 32 steps are fetched at once (lane l holds step t0 + l, the next 32 steps are in flight
+// while these run) and a step broadcasts its words with one shuffle each.
+template <int POLICY, int RT>
 __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
     const int lane = threadIdx.x & 31;
     const int fidx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (fidx >= a.count) return;                                   // whole warps leave together
     const int frame = a.frame0 + fidx;
     const CodecParams& c = a.c;
-    const int R = c.R;
+    const int R = RT ? RT : c.R;
+    constexpr int SYMB = (POLICY == P_WY_U16) ? 2 : 1;
+    constexpr int WPS = RT ? (RT * SYMB + 3) / 4 : (MAX_R * SYMB + 3) / 4;     // 32-bit words per step
+    const int step_bytes = R * SYMB;
     uint16_t* gm = a.metrics + (size_t)frame * 64;
     int lo = gm[lane], hi = gm[lane + 32];
     if (PolicyTraits<POLICY>::is_signed16) { lo = (int16_t)lo; hi = (int16_t)hi; }
     const unsigned cw = a.cw[lane];                                // code word of butterfly `lane` (host table)
     const unsigned char* sp = (const unsigned char*)a.syms + (size_t)frame * a.sym_stride;
-    const int step_bytes = R * c.sym_bytes;
     uint32_t* drow = a.dec + ((size_t)frame * a.dec_rows + a.step0) * 2;
     const int src0 = lane >> 1, src1 = 16 + (lane >> 1);
     const bool odd = lane & 1;
-    for (int t = 0; t < a.nsteps; t++) {
-        int sym[MAX_R];
-        const void* p = sp + (size_t)t * step_bytes;
-        for (int i = 0; i < R; i++) sym[i] = load_symbol<POLICY>(p, i);
-        const int bm = branch_metric<POLICY>(c, cw, sym);
-        int v0, v1, d0, d1;
-        acs<POLICY>(c.max_error, lo, hi, bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
-        const unsigned w0 = __ballot_sync(0xffffffffu, d0), w1 = __ballot_sync(0xffffffffu, d1);
-        const int a0 = __shfl_sync(0xffffffffu, v0, src0), a1 = __shfl_sync(0xffffffffu, v1, src0);
-        const int c0 = __shfl_sync(0xffffffffu, v0, src1), c1 = __shfl_sync(0xffffffffu, v1, src1);
-        lo = odd ? a1 : a0;
-        hi = odd ? c1 : c0;
-        if (lane == 0) *reinterpret_cast<uint2*>(drow + 2 * (size_t)t) = make_uint2(w0, w1);
-        if (PolicyTraits<POLICY>::has_renorm) {
-            const int m0 = __shfl_sync(0xffffffffu, lo, 0);
-            if (renorm_needed<POLICY>(c, m0)) {                     // uniform over the warp
-                const int mn = __reduce_min_sync(0xffffffffu, min(lo, hi));
-                lo = renorm_apply<POLICY>(lo, mn);
-                hi = renorm_apply<POLICY>(hi, mn);
+
+    auto fetch = [&](uint32_t (&buf)[WPS], int t0) {              // this lane's step of the 32 starting at t0
+        const int t = t0 + lane;
+#pragma unroll
+        for (int w = 0; w < WPS; w++) buf[w] = 0;
+        if (t < a.nsteps) {
+            const unsigned char* p = sp + (size_t)t * step_bytes;
+#pragma unroll
+            for (int j = 0; j < WPS * 4; j++)
+                if (j < step_bytes) buf[j >> 2] |= (uint32_t)__ldg(p + j) << ((j & 3) * 8);
+        }
+    };
+    uint32_t cur[WPS], nxt[WPS];
+    fetch(cur, 0);
+    for (int t0 = 0; t0 < a.nsteps; t0 += 32) {
+        fetch(nxt, t0 + 32);
+        const int nhere = min(32, a.nsteps - t0);
+        for (int i = 0; i < nhere; i++) {
+            uint32_t sw[WPS];
+#pragma unroll
+            for (int w = 0; w < WPS; w++) sw[w] = __shfl_sync(0xffffffffu, cur[w], i);
+            int sym[RT ? RT : MAX_R];
+#pragma unroll
+            for (int r = 0; r < (RT ? RT : MAX_R); r++) {
+                if (r < R) {
+                    const int bpos = r * SYMB;
+                    const uint32_t v = sw[bpos >> 2] >> ((bpos & 3) * 8);
+                    sym[r] = (POLICY == P_WY_U16) ? (int)(int16_t)(v & 0xffffu)
+                           : (POLICY == P_WY_U8) ? (int)(int8_t)(v & 0xffu) : (int)(v & 0xffu);
+                }
+            }
+            const int bm = branch_metric_rt<POLICY, RT>(c, cw, sym);
+            int v0, v1, d0, d1;
+            acs<POLICY>(c.max_error, lo, hi, bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
+            const unsigned w0 = __ballot_sync(0xffffffffu, d0), w1 = __ballot_sync(0xffffffffu, d1);
+            const int a0 = __shfl_sync(0xffffffffu, v0, src0), a1 = __shfl_sync(0xffffffffu, v1, src0);
+            const int c0 = __shfl_sync(0xffffffffu, v0, src1), c1 = __shfl_sync(0xffffffffu, v1, src1);
+            lo = odd ? a1 : a0;
+            hi = odd ? c1 : c0;
+            if (lane == 0) *reinterpret_cast<uint2*>(drow + 2 * (size_t)(t0 + i)) = make_uint2(w0, w1);
+            if (PolicyTraits<POLICY>::has_renorm) {
+                const int m0 = __shfl_sync(0xffffffffu, lo, 0);
+                if (renorm_needed<POLICY>(c, m0)) {                     // uniform over the warp
+                    const int mn = __reduce_min_sync(0xffffffffu, min(lo, hi));
+                    lo = renorm_apply<POLICY>(lo, mn);
+                    hi = renorm_apply<POLICY>(hi, mn);
+                }
             }
         }
+#pragma unroll
+        for (int w = 0; w < WPS; w++) cur[w] = nxt[w];
     }
     gm[lane] = (uint16_t)lo;
     gm[lane + 32] = (uint16_t)hi;
@@ -67,7 +135,13 @@ template <int POLICY>
 cudaError_t launch_policy(const GenericArgs& a, cudaStream_t st) {
     const int warps_per_block = 4;
     const int blocks = (a.count + warps_per_block - 1) / warps_per_block;
-    acs_k7_warp_kernel<POLICY><<<blocks, warps_per_block * 32, 0, st>>>(a);
+    const dim3 g(blocks), b(warps_per_block * 32);
+    switch (a.c.R) {
+    case 2: acs_k7_warp_kernel<POLICY, 2><<<g, b, 0, st>>>(a); break;
+    case 3: acs_k7_warp_kernel<POLICY, 3><<<g, b, 0, st>>>(a); break;
+    case 4: acs_k7_warp_kernel<POLICY, 4><<<g, b, 0, st>>>(a); break;
+    default: acs_k7_warp_kernel<POLICY, 0><<<g, b, 0, st>>>(a); break;
+    }
     return cudaGetLastError();
 }
 

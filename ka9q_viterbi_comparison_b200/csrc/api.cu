@@ -157,6 +157,7 @@ struct b200v_batch {
     int* d_scan = nullptr;       // wy-u16 symbol range check
     K24GraphCache k24_graph;     // K=24: captured step loop of the last update call
     bool user_variant = false;   // set_variant() was called: no automatic family changes
+    int tb_mode = 0, tb_warmup = 0;   // b200v_batch_set_traceback
     // lazily allocated staging for the host-pointer entry points
     void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
     uint8_t* d_out_stage = nullptr; size_t out_stage_bytes = 0;
@@ -186,7 +187,16 @@ static int create_impl(b200v_batch* h, int starting_state);
 
 // automatic kernel family: the specialised one where it exists; otherwise warp-per-frame for K=7 (any polynomial
 // set, ~4x the generic kernel), else the generic shared-memory kernel. Families 1 and 3 share the decision layout.
-static int fallback_variant(const b200v_batch* h) { return h->has_fast ? 2 : k7_warp_supported(h->c) ? 3 : 1; }
+// Small K=7 batches -- down to the single frame of the reference's own benchmark loop (src/main.cpp:264-278) -- are
+// latency-bound: a frame that owns a warp advances a step in ~70 ns against ~200 ns for a frame that owns one thread
+// of the register kernel (measured, 8198-step frames: 1 frame 0.58 vs 1.63 ms, 1024 frames 2.7 vs 3.6 ms including
+// the upload, equal at 4096 frames), so up to 2048 frames the warp-per-frame family is the automatic choice.
+constexpr int K7_WARP_MAX_FRAMES = 2048;
+static int fallback_variant(const b200v_batch* h) {
+    if (k7_warp_supported(h->c) && (!h->has_fast || h->n_frames <= K7_WARP_MAX_FRAMES)) return 3;
+    return h->has_fast ? 2 : 1;
+}
+static int layout_of_variant(const b200v_batch* h, int variant) { return variant == 2 ? h->fast_layout : DL_BALLOT_FRAME_MAJOR; }
 static int exact_variant(const b200v_batch* h) { return k7_warp_supported(h->c) ? 3 : 1; }
 
 extern "C" b200v_batch* b200v_batch_create(int codec, int K, int R, const int* poly, int frame_steps,
@@ -205,6 +215,10 @@ extern "C" b200v_batch* b200v_batch_create(int codec, int K, int R, const int* p
     b200v_batch* h = new (std::nothrow) b200v_batch();
     if (!h) { fail(B200V_ERR_NOMEM, "host allocation failed"); return nullptr; }
     h->codec = codec; h->c = c; h->n_frames = n_frames; h->frame_steps = frame_steps; h->device = device;
+    if (const char* e = getenv("B200V_TRACEBACK")) {     // initial b200v_batch_set_traceback mode (A/B measurements)
+        const int m = atoi(e);
+        if (m >= 0 && m <= 2) h->tb_mode = m;
+    }
     if (create_impl(h, 0) != B200V_OK) { free_all(h); return nullptr; }
     return h;
 }
@@ -263,7 +277,7 @@ static int create_impl(b200v_batch* h, int starting_state) {
                      smallk_supported(c) ? DL_SMALLK_INTERLEAVED : DL_BALLOT_FRAME_MAJOR;
     h->has_fast = h->fast_layout != DL_BALLOT_FRAME_MAJOR;
     h->variant = fallback_variant(h);
-    h->layout = h->fast_layout;
+    h->layout = layout_of_variant(h, h->variant);
     return b200v_batch_init(h, starting_state);
 }
 
@@ -286,6 +300,13 @@ extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
 }
 extern "C" int b200v_batch_get_variant(const b200v_batch* h) { return h ? h->variant : 0; }
 
+extern "C" int b200v_batch_set_traceback(b200v_batch* h, int mode, int warmup_rows) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (mode < 0 || mode > 2 || warmup_rows < 0) return fail(B200V_ERR_ARG, "traceback mode %d / warm-up %d", mode, warmup_rows);
+    h->tb_mode = mode; h->tb_warmup = warmup_rows;
+    return B200V_OK;
+}
+
 extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     CUDA_TRY(cudaSetDevice(h->device));
@@ -295,7 +316,7 @@ extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     h->cur_metrics = 0;
     if (!h->user_variant && h->layout != DL_CANONICAL) {     // back to the automatic family (wy-u16 may have left it)
         h->variant = fallback_variant(h);
-        h->layout = h->has_fast ? h->fast_layout : DL_BALLOT_FRAME_MAJOR;
+        h->layout = layout_of_variant(h, h->variant);
     }
     return B200V_OK;
 }
@@ -439,13 +460,17 @@ extern "C" int b200v_batch_update(b200v_batch* h, const void* syms, size_t frame
 }
 
 static int launch_chainback_range(b200v_batch* h, uint8_t* d_data, size_t stride, unsigned nbits, unsigned endstate,
-                                  int f0, int cnt, cudaStream_t st, const unsigned* endstates = nullptr) {
+                                  int f0, int cnt, cudaStream_t st, const unsigned* endstates = nullptr,
+                                  bool pipelined = false) {
     ChainbackArgs a{};
     a.c = h->c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
     a.row_phase = h->d_row_phase;
     a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
     a.metrics = h->cur_metrics ? h->d_metrics2 : h->d_metrics; a.out = d_data; a.out_stride = stride;
     a.nbits = nbits; a.endstate = endstate; a.endstates = endstates; a.results = h->d_results;
+    // chunks of the pipelined host-buffer decode run beside other chunks' kernels and copies: throughput, not
+    // latency, so they keep the per-frame kernels (measured: K=7 65536 frames e2e 17.4 vs 10.3 Gbit/s)
+    a.par_mode = (pipelined && h->tb_mode == 0) ? 1 : h->tb_mode; a.par_warmup = h->tb_warmup;
     CUDA_TRY(launch_chainback(a, st));
     h->launches++;
     return B200V_OK;
@@ -564,7 +589,7 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
                                  (size_t)cnt * srow, cudaMemcpyHostToDevice, st));
         rc = launch_update_range(h, h->d_syms_stage, srow, nsteps, 0, f0, cnt, st);
         if (rc) return rc;
-        rc = launch_chainback_range(h, h->d_out_stage, orow, nbits, 0, f0, cnt, st);
+        rc = launch_chainback_range(h, h->d_out_stage, orow, nbits, 0, f0, cnt, st, nullptr, true);
         if (rc) return rc;
         CUDA_TRY(cudaMemcpyAsync(data + (size_t)f0 * orow, h->d_out_stage + (size_t)f0 * orow, (size_t)cnt * orow,
                                  cudaMemcpyDeviceToHost, st));

@@ -88,6 +88,91 @@ __global__ void __launch_bounds__(128) chainback_k7_kernel(const ChainbackArgs a
     }
 }
 
+// ---- speculative block-parallel traceback (small and medium batches) -----------------------------------------
+// The traceback is a pointer chase: one dependent decision-bit load per decoded bit, ~100-270 ns each when a
+// frame has the GPU to itself (8192 bits: ~0.9 ms through main.cpp's chainback call; the reference CPU: 12 us).
+// It parallelises exactly: the state after K-1 backward steps consists of the last K-1 decision bits only, so two
+// traces that ever hold the same state at the same row stay identical. One CUDA block per frame; thread b decodes
+// bits [b*L, (b+1)*L). It starts D rows further up from a guessed state (0) -- or from the true end state when that
+// point is the end of the frame -- and walks down; after the D warm-up rows its state has merged with the true
+// survivor with overwhelming probability. The guess is then VERIFIED: thread b's state on entering its own bits
+// must equal the state thread b+1 left its bits with. The topmost thread is exact by construction, so if every
+// boundary matches, every thread traced the reference's path (induction downwards) and the output is bit-exact. On
+// a mismatch the failing threads re-trace their own bits from the state the thread above handed down, and the
+// check repeats: each round makes at least the highest failing block exact, so it terminates (worst case: as many
+// dependent steps as the sequential kernel).
+template <int LAYOUT> struct ParReader {
+    DecisionReader<LAYOUT> rd;
+    __device__ ParReader(const ChainbackArgs& a, int f, const uint8_t*) : rd(a, f) {}
+    __device__ __forceinline__ unsigned bit(unsigned row, unsigned state) const { return rd.bit(row, state); }
+};
+template <> struct ParReader<DL_K7_INTERLEAVED> {
+    DecisionReader<DL_K7_INTERLEAVED> rd;
+    __device__ ParReader(const ChainbackArgs& a, int f, const uint8_t* tab) : rd(a, f, tab) {}
+    __device__ __forceinline__ unsigned bit(unsigned row, unsigned state) const { return rd.bit_of(rd.load(row), row, state); }
+};
+
+template <int LAYOUT>
+__global__ void __launch_bounds__(1024) chainback_par_kernel(const ChainbackArgs a, const unsigned L, const unsigned D) {
+    extern __shared__ unsigned s_exit[];                 // state each thread left its bits with
+    __shared__ uint8_t tab[LAYOUT == DL_K7_INTERLEAVED ? k7::NB * k7::S : 1];
+    if (LAYOUT == DL_K7_INTERLEAVED) fill_k7_table(tab, a.c.policy);
+    const unsigned B = blockDim.x, b = threadIdx.x;
+    const int f = a.frame0 + blockIdx.x;
+    const unsigned K1 = (unsigned)(a.c.K - 1), N = a.nbits;
+    const ParReader<LAYOUT> rd(a, f, tab);
+    uint8_t* out = a.out + (size_t)f * a.out_stride;
+    const unsigned end_state = (a.endstates ? a.endstates[f] : a.endstate) % (unsigned)a.c.S;
+    if (b == 0) {
+        if (a.results) a.results[f] = a.c.policy == P_KA9Q_S16_615 ? (int)(int16_t)a.metrics[(size_t)f * a.c.S + end_state] : 0;
+    }
+    const unsigned lo = b * L, hi = min(N, lo + L);      // this thread's decoded bits (lo < N for every thread)
+    const unsigned n0 = min(N, hi + D);
+    unsigned s = n0 == N ? end_state : 0u;
+    for (unsigned n = n0; n-- > hi;) s = (s >> 1) | (rd.bit(n + K1, s) << (K1 - 1));
+    unsigned entry = s;
+    bool redo = true;
+    for (;;) {
+        if (redo) {
+            unsigned cur = 0;
+            for (unsigned n = hi; n-- > lo;) {
+                const unsigned k = rd.bit(n + K1, s);
+                s = (s >> 1) | (k << (K1 - 1));
+                cur = (cur >> 1) | (k << 7);
+                if ((n & 7u) == 0) out[n >> 3] = (uint8_t)cur;
+            }
+            s_exit[b] = s;
+        }
+        __syncthreads();
+        // verification: the state this thread entered its bits with must be the state the thread above left with.
+        // The topmost thread is exact, so the highest failing thread is repaired by one re-trace from that state:
+        // every round extends the exact prefix by at least one block (usually all of them), at most B rounds.
+        const unsigned want = b + 1 < B ? s_exit[b + 1] : entry;
+        redo = want != entry;
+        if (!__syncthreads_or(redo)) break;              // also orders this round's reads before the next writes
+        s = entry = want;
+    }
+}
+
+// geometry of the block-parallel traceback for `count` frames of `nbits` bits, or false: use the per-frame kernels
+static bool par_geometry(const ChainbackArgs& a, unsigned& L, unsigned& D, unsigned& B) {
+    if (a.par_mode == 1 || a.c.policy == P_KA9Q_S16_224 || (a.nbits & 7u) || a.nbits < 64u) return false;
+    const bool forced = a.par_mode == 2;
+    // automatic choice: while a frame-at-a-time traceback is latency-bound, i.e. up to ~16 Mi decoded bits per
+    // launch (measured, 2048-bit frames: K=15 1024 frames 1.57 -> 0.35 ms, K=9 4096 frames 1.10 -> 0.74 ms, 8192
+    // frames 1.19 -> 1.00 ms); beyond that the per-frame kernels are bandwidth-bound and read each row once
+    if (!forced && (unsigned long long)a.count * a.nbits > (1ull << 24)) return false;
+    unsigned budget = min(1024u, (262144u / (unsigned)a.count) & ~31u);            // threads per frame
+    if (forced) budget = max(budget, 32u);
+    if (budget < 32u) return false;
+    D = a.par_warmup > 0 ? (unsigned)a.par_warmup : max(64u, 12u * (unsigned)(a.c.K - 1));
+    D = (D + 7u) & ~7u;
+    const unsigned Lmin = forced ? 8u : 32u;
+    L = max(Lmin, ((a.nbits + budget - 1) / budget + 7u) & ~7u);
+    B = (a.nbits + L - 1) / L;
+    return forced ? B >= 2u : (B >= 4u && 4u * (L + D) <= a.nbits);
+}
+
 // smallest path metric of every frame: one block per frame, packed (key << 32 | state) minimum
 __global__ void best_state_kernel(const CodecParams c, const uint16_t* metrics, unsigned* best) {
     const int f = blockIdx.x;
@@ -127,6 +212,19 @@ cudaError_t launch_best_state(const CodecParams& c, const uint16_t* metrics, uns
 
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st) {
     if (a.count <= 0) return cudaSuccess;
+    unsigned L, D, B;
+    if (par_geometry(a, L, D, B)) {
+        const size_t sm = (size_t)B * sizeof(unsigned);
+        switch (a.layout) {
+        case DL_BALLOT_FRAME_MAJOR: chainback_par_kernel<DL_BALLOT_FRAME_MAJOR><<<a.count, B, sm, st>>>(a, L, D); break;
+        case DL_K7_INTERLEAVED: chainback_par_kernel<DL_K7_INTERLEAVED><<<a.count, B, sm, st>>>(a, L, D); break;
+        case DL_GRP_INTERLEAVED: chainback_par_kernel<DL_GRP_INTERLEAVED><<<a.count, B, sm, st>>>(a, L, D); break;
+        case DL_CANONICAL: chainback_par_kernel<DL_CANONICAL><<<a.count, B, sm, st>>>(a, L, D); break;
+        case DL_SMALLK_INTERLEAVED: chainback_par_kernel<DL_SMALLK_INTERLEAVED><<<a.count, B, sm, st>>>(a, L, D); break;
+        default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
     const int threads = 128;
     const int blocks = (a.count + threads - 1) / threads;
     switch (a.layout) {

@@ -81,6 +81,7 @@ struct ChainbackArgs {
     unsigned nbits, endstate;
     const unsigned* endstates;  // per-frame end states (device, [n_frames]) or nullptr: use `endstate` for all
     int* results;               // device [n_frames] or nullptr
+    int par_mode, par_warmup;   // b200v_batch_set_traceback: 0 auto / 1 per-frame threads / 2 block-parallel; warm-up rows or 0
 };
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st);
 // best[f] = index of the smallest path metric of frame f (ties: lowest state); ka9q modular metrics are compared

@@ -424,18 +424,22 @@ def test_wy_u16_out_of_range_symbols_take_the_generic_family(name):
     T = 90 if K == 15 else 300
     nbits = T - (K - 1)
     rng = np.random.default_rng(16)
-    in_range = rng.integers(-127, 128, size=(3, T * R)).astype(np.int16)
+    # K=7: batches of up to 2048 frames run on the warp-per-frame family anyway (exact for any input), so the
+    # routing away from the register kernel needs a larger batch; frames 3.. repeat the first three
+    n_frames = 2051 if K == 7 else 3
+    in_range = np.resize(rng.integers(-127, 128, size=(3, T * R)), (n_frames, T * R)).astype(np.int16)
     wild = rng.integers(-32768, 32768, size=(3, T * R)).astype(np.int16)
     wild[1, ::7] = -32768
     wild[2, ::5] = 32767
-    with kv.BatchDecoder(codec, T, 3, K=K, R=R) as dec:
+    wild = np.resize(wild, (n_frames, T * R)).astype(np.int16)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
         exact = 3 if K == 7 else 1     # the exact-for-any-input family: warp-per-frame for K=7, else generic
         for syms, expect_variant in ((in_range, 2), (wild, exact), (in_range, 2)):
             dec.reset()
             dec.update(syms)
             assert dec.variant == expect_variant
             out = dec.chainback(nbits)
-            for f in range(3):
+            for f in (0, 1, 2, n_frames - 1):
                 q = o.Oracle(c, T)
                 qo, qd = q.decode(syms[f], nbits)
                 assert np.array_equal(dec.decisions(f, 0, T), qd), (expect_variant, f)
@@ -529,7 +533,7 @@ def test_common_codes(code, width):
         refs.append((q.decisions(0, T), q.metrics(), q.chainback(nbytes * 8, 0)))
         q.close()
     with kv.BatchDecoder(kv.WY_U8 if width == 8 else kv.WY_U16, T, n_frames, K=K, R=R, poly=poly) as dec:
-        assert dec.variant == 2, "every common code has a specialised kernel family"
+        assert dec.variant == (3 if K == 7 else 2), "every common code has a specialised kernel family (small K=7 batches: warp per frame)"
         for v in variants(dec):
             dec.reset()
             dec.set_variant(v)
@@ -553,6 +557,7 @@ def test_modular_policy_long_update_rebases_the_unwrapped_lanes(name):
     T = nbytes * 8 + K - 1            # 5608 / 5606 steps: past two rebase points of the K=9 kernel
     data, syms = make_batch(c, n_frames, nbytes, 0.9, seed=0x10E6)
     with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        dec.set_variant(2)        # the register / group kernels (a batch this small would default to family 3 for K=7)
         assert dec.variant == 2
         dec.reset()
         dec.update(syms)
@@ -565,3 +570,64 @@ def test_modular_policy_long_update_rebases_the_unwrapped_lanes(name):
             assert np.array_equal(dec.metrics(f), q.metrics()), f"frame {f}: metrics"
             assert np.array_equal(out[f], q.chainback(nbytes * 8, 0)), f"frame {f}: decoded bytes"
             q.close()
+
+
+@pytest.mark.parametrize("name", ["ka9q27", "spiral27", "wy_sse_u16_k7r4", "ka9q29", "spiral49", "wy_sse_u8_k9r2",
+                                  "ka9q615", "spiral615", "wy_sse_u8_k15r6"])
+def test_block_parallel_traceback_is_bit_exact(name):
+    """b200v_batch_set_traceback: the speculative block-parallel chainback (mode 2) against the one-thread-per-frame
+    kernels (mode 1) and the oracle, for every kernel family / decision layout, at the default warm-up, at a warm-up
+    far too short to merge (8 rows: many boundaries fail verification and take the sequential re-trace) and with a
+    non-zero end state. Noisy frames (sigma = 1.0) so that survivor paths really differ between start states."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes = 64 if K == 15 else 160
+    n_frames = 3 if K == 15 else 11
+    nbits = nbytes * 8
+    T = nbits + K - 1
+    data, syms = make_batch(c, n_frames, nbytes, 1.0, seed=0x7B)
+    refs = {}
+    for end in (0, 5):
+        for f in range(n_frames):
+            q = o.Oracle(c, T)
+            q.init(0)
+            q.update(syms[f], T)
+            refs[(end, f)] = q.chainback(nbits, end, return_code=True)
+            q.close()
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        for v in variants(dec):
+            dec.reset()
+            dec.set_variant(v)
+            dec.reset()
+            dec.update(syms)
+            for mode, warm in ((1, 0), (2, 0), (2, 8), (2, 1000), (0, 0)):
+                dec.set_traceback(mode, warm)
+                for end in (0, 5):
+                    out = dec.chainback(nbits, end)
+                    rcs = dec.chainback_results()
+                    for f in range(n_frames):
+                        qo, qrc = refs[(end, f)]
+                        assert np.array_equal(out[f], qo), f"v{v} mode {mode} warm-up {warm} end {end} frame {f}"
+                        assert int(rcs[f]) == qrc
+        with pytest.raises(kv.B200ViterbiError):
+            dec.set_traceback(3, 0)
+        dec.set_traceback(0, 0)
+
+
+def test_block_parallel_traceback_main_cpp_frames():
+    """main.cpp's own frame lengths (1024 / 512 / 256 bytes, noiseless symbols, one frame): the automatic traceback
+    choice is the block-parallel kernel there; decoded bytes equal the transmitted ones and the sequential kernel's."""
+    for name in ("ka9q27", "spiral47", "ka9q29", "spiral615", "wy_sse_u16_k15r6"):
+        codec, K, R = CASES[name]
+        c = o.codec_by_name(name)
+        nbytes = {7: 1024, 9: 512, 15: 256}[K]
+        T = nbytes * 8 + K - 1
+        data, syms = make_batch(c, 1, nbytes, 0.0, seed=0xC0DE)
+        with kv.BatchDecoder(codec, T, 1, K=K, R=R) as dec:
+            dec.reset()
+            dec.update(syms)
+            auto = dec.chainback(nbytes * 8)
+            dec.set_traceback(1)
+            seq = dec.chainback(nbytes * 8)
+            assert np.array_equal(auto, seq), name
+            assert np.array_equal(auto, data), name
