@@ -158,17 +158,24 @@ __global__ void __launch_bounds__(1024) chainback_par_kernel(const ChainbackArgs
 static bool par_geometry(const ChainbackArgs& a, unsigned& L, unsigned& D, unsigned& B) {
     if (a.par_mode == 1 || a.c.policy == P_KA9Q_S16_224 || (a.nbits & 7u) || a.nbits < 64u) return false;
     const bool forced = a.par_mode == 2;
-    // automatic choice: while a frame-at-a-time traceback is latency-bound, i.e. up to ~16 Mi decoded bits per
-    // launch (measured, 2048-bit frames: K=15 1024 frames 1.57 -> 0.35 ms, K=9 4096 frames 1.10 -> 0.74 ms, 8192
-    // frames 1.19 -> 1.00 ms); beyond that the per-frame kernels are bandwidth-bound and read each row once
-    if (!forced && (unsigned long long)a.count * a.nbits > (1ull << 24)) return false;
     unsigned budget = min(1024u, (262144u / (unsigned)a.count) & ~31u);            // threads per frame
     if (forced) budget = max(budget, 32u);
-    if (budget < 32u) return false;
+    if (budget < 32u) return false;          // more than 8192 frames per launch: enough independent chases in flight already
     D = a.par_warmup > 0 ? (unsigned)a.par_warmup : max(64u, 12u * (unsigned)(a.c.K - 1));
     D = (D + 7u) & ~7u;
     const unsigned Lmin = forced ? 8u : 32u;
     L = max(Lmin, ((a.nbits + budget - 1) / budget + 7u) & ~7u);
+    // Automatic choice. Up to ~16 Mi decoded bits per launch a frame-at-a-time traceback is purely latency-bound and
+    // the warm-up rows cost nothing (measured, 2048-bit frames: K=15 1024 frames 1.57 -> 0.35 ms, K=9 4096 frames
+    // 1.10 -> 0.74 ms). Larger launches are limited by 32-byte sectors fetched per decision bit, so there the bits
+    // of a block are at least as many as its warm-up rows (at most 2x the sectors of the per-frame kernels):
+    // 16384-bit frames, K=15 x 2048 frames 12.3 -> 1.9 ms, K=9 x 4096 frames 9.4 -> 2.6 ms.
+    // The K=7 register layout keeps its per-frame kernel there: it streams whole rows, coalesced (4096 frames x
+    // 16384 bits: 2.17 ms against 2.36 ms block-parallel).
+    if (!forced && (unsigned long long)a.count * a.nbits > (1ull << 24)) {
+        if (a.layout == DL_K7_INTERLEAVED) return false;
+        L = max(L, D);
+    }
     B = (a.nbits + L - 1) / L;
     return forced ? B >= 2u : (B >= 4u && 4u * (L + D) <= a.nbits);
 }
