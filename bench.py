@@ -128,6 +128,24 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------
 # CPU reference arm: the reference's own decoder on the host cores (oracle/_ref, else the oracle port)
 # ---------------------------------------------------------------------------------------------------
+def cpu_model():
+    """model name and logical / physical core counts of the host the CPU arm runs on"""
+    model, cores = "unknown CPU", set()
+    try:
+        phys = core = None
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name") and model == "unknown CPU":
+                model = line.split(":", 1)[1].strip()
+            elif line.startswith("physical id"):
+                phys = line.split(":", 1)[1].strip()
+            elif line.startswith("core id"):
+                core = line.split(":", 1)[1].strip()
+                cores.add((phys, core))
+    except OSError:
+        pass
+    return f"{model}, {os.cpu_count()} threads / {len(cores) or '?'} cores"
+
+
 def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None, K=7, R=2):
     """Decode frames of `frame_bits` with one decoder instance per host thread for ~`seconds`.
     Returns (Mbit/s aggregate, threads, kind, sample description)."""
@@ -171,7 +189,7 @@ def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None, K=7, R
         d.close()
     frames = sum(counts)
     return frames * frame_bits / dt / 1e6, n_threads, kind, \
-        f"{frames} frames x {frame_bits} bits of {name}, sigma={sigma}, {n_threads} threads, {dt:.1f} s"
+        f"{frames} frames x {frame_bits} bits of {name}, sigma={sigma}, {n_threads} threads, {dt:.1f} s, host {cpu_model()}"
 
 
 def run_reference_arm(args):

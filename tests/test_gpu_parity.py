@@ -474,8 +474,9 @@ def test_wy_hard8_config(name):
                 q.close()
 
 
+@pytest.mark.parametrize("tail", [False, True], ids=["ragged_bits", "byte_multiple"])
 @pytest.mark.parametrize("name", ["ka9q27", "spiral29", "ka9q615", "wy_sse_u16_k7r2", "ka9q29"])
-def test_best_state_traceback_of_unterminated_streams(name):
+def test_best_state_traceback_of_unterminated_streams(name, tail):
     """b200v_batch_chainback_best_dev: no tail, every frame traced from its own smallest path metric. Checked
     against the oracle's metrics (argmin, ties to the lowest state; modular metrics as int8 distances from state 0)
     and the oracle's chainback from that state; at low noise the decoded bits are the transmitted ones."""
@@ -483,13 +484,17 @@ def test_best_state_traceback_of_unterminated_streams(name):
     codec, K, R = CASES[name]
     c = o.codec_by_name(name)
     nbytes, n_frames = (6, 3) if K == 15 else (40, 9)
-    T = nbytes * 8                                     # unterminated: only the data bits' steps are fed
+    if tail:                                           # nbits a multiple of 8: the block-parallel traceback (forced:
+        nbytes = 16 if K == 15 else 80                 # these frames are short) starts its top block from per-frame states
+    T = nbytes * 8 + (K - 1 if tail else 0)            # unterminated: only the data bits' steps are fed (no tail)
     nbits = T - (K - 1)
-    data, syms = make_batch(c, n_frames, nbytes, 0.3, seed=31)
+    data, syms = make_batch(c, n_frames, nbytes + (2 if tail else 0), 0.3, seed=31)   # cut before the frame's end
     syms = np.ascontiguousarray(syms[:, :T * R])
     with kv.BatchDecoder(codec, T + K - 1, n_frames, K=K, R=R) as dec:
         dec.reset()
         dec.update(syms)
+        if tail:
+            dec.set_traceback(2, 16)
         d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
         d_best = torch.zeros(n_frames, dtype=torch.int32, device="cuda")
         dec.chainback_best_dev(d_out, nbytes, nbits, d_best)
@@ -631,3 +636,32 @@ def test_block_parallel_traceback_main_cpp_frames():
             seq = dec.chainback(nbytes * 8)
             assert np.array_equal(auto, seq), name
             assert np.array_equal(auto, data), name
+
+
+@pytest.mark.parametrize("name", ["ka9q29", "spiral49", "ka9q615", "spiral27"])
+def test_long_frames_16384_bits_block_parallel_traceback(name):
+    """BASELINE configs[3]'s long frames (16384 bits): the automatic traceback is the block-parallel kernel; decoded
+    bytes, chainback return values and final metrics against the oracle at sigma = 1.0 / 0.7."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes = 2048
+    n_frames = 2 if K == 15 else 6
+    T = nbytes * 8 + K - 1
+    data, syms = make_batch(c, n_frames, nbytes, 1.0 if K == 15 else 0.7, seed=0x16384)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        dec.reset()
+        dec.update(syms)
+        out = dec.chainback(nbytes * 8)
+        rcs = dec.chainback_results()
+        dec.set_traceback(1)
+        seq = dec.chainback(nbytes * 8)
+        assert np.array_equal(out, seq)
+        for f in range(n_frames):
+            q = o.Oracle(c, T)
+            q.init(0)
+            q.update(syms[f], T)
+            qo, qrc = q.chainback(nbytes * 8, 0, return_code=True)
+            assert np.array_equal(out[f], qo), f
+            assert int(rcs[f]) == qrc
+            assert np.array_equal(dec.metrics(f), q.metrics()), f
+            q.close()
