@@ -24,6 +24,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "decoded Mbit/s (update+chainback)"
 UNIT = "Mbit/s"
+ISSUE_PEAK = 148 * 4 * 1.965e9      # warp-instructions/s: one issue slot per SM sub-partition and clock
 ALU_PEAK = 148 * 128 * 1.965e9      # dual-pipe integer issue peak, thread-instructions/s (measured 96-121 of 128 lanes)
 
 
@@ -362,12 +363,14 @@ def run_b200_arm(args):
     bytes_per_step_frame = R * sym_bytes + S / 8.0
     achieved = frames * T * bytes_per_step_frame / (upd * 1e-3) / 1e9
     lane_ops = frames * T * 4.0 * S                      # 4*S integer lane-ops per step
-    traffic, traffic_src = None, None
+    traffic, traffic_src, warp_inst = None, None, None
     try:     # DRAM bytes per launch as ncu measured them (profiles/ncu_traffic.json: per frame-step, scaled to this launch)
         tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(
             f"{args.codec}_k{K}r{R}" if args.codec.startswith("wy_") else args.codec)
         if tr:
             traffic, traffic_src = tr["bytes_per_frame_step"] * frames * T, tr["capture"]
+            if tr.get("warp_inst_per_frame_step"):
+                warp_inst = tr["warp_inst_per_frame_step"] * frames * T
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
@@ -377,7 +380,11 @@ def run_b200_arm(args):
                 # per clock and SM at the measured SM clock limit (tools/ubench_int.cu, profiles/r01_ubench_int_pipes.jsonl)
                 "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "peak_lane_ops_per_s": ALU_PEAK,
                         "frac": lane_ops / (upd * 1e-3) / ALU_PEAK,
-                        "note": "4*S integer lane-ops per trellis step (SURVEY 8d) vs 148 SMs x 128 lanes/clk x 1.965 GHz"}}
+                        # executed warp-instructions (ncu count of the same kernel, scaled to this launch) per issue slot
+                        "issue_frac": (warp_inst / (upd * 1e-3) / ISSUE_PEAK) if warp_inst else None,
+                        "note": "frac: 4*S scalar lane-ops per trellis step (SURVEY 8d) vs 148 SMs x 128 thread-instructions/clk "
+                                "x 1.965 GHz -- packed u16x2 instructions carry two lanes, so frac can exceed 1; issue_frac: "
+                                "warp-instructions ncu counted for this kernel / (148 x 4 issue slots x 1.965 GHz x kernel time)"}}
 
     cpu = None
     if not args.no_cpu_baseline:

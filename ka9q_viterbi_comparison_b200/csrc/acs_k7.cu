@@ -112,7 +112,22 @@ struct K7Args {
     int C, thr, soft_hi, soft_lo;
     int one, neg1;                 // 1 and -1, opaque to ptxas: multipliers that keep plain adds on the FMA pipe
     int zero;                      // 0, opaque to ptxas: third operand that keeps an add on the ALU pipe (IADD3)
+    unsigned* done;                // SIGNAL kernels: done[block] += 1 per warp once the block's decision rows are written
 };
+
+// Block-completion counter (release pattern: warp barrier, gpu-scope fence, relaxed atomic): lets a consumer on
+// another stream see which blocks' decision rows are in memory. Its other effect is the reason the ka9q27 instance
+// always uses it: with these few extra instructions ptxas allocates 72 registers WITHOUT spills (7 resident blocks
+// per SM, 28 warps) where the plain kernel takes 78 (6 blocks) and __launch_bounds__(128, 7) spills 116 bytes
+// (45 ms): 15.90 -> 14.04 ms per 1 Mi frames, bit-identical output (profiles/r01d_k7_signal_variant.txt).
+
+__device__ __forceinline__ void signal_done(unsigned* done) {
+    __syncwarp(__activemask());
+    if ((threadIdx.x & 31) == 0) {
+        __threadfence();
+        atomicAdd(done + blockIdx.x, 1u);
+    }
+}
 
 // ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
 template <int POLICY, class CODE, int P, int KK>
@@ -280,7 +295,9 @@ __device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE
     step<POLICY, CODE, P>(w, sym, a, off, dec_row);
 }
 
-template <int POLICY, class CODE>
+// (__launch_bounds__(128, 6) for the saturating policies -- 80 registers, 8-16 bytes of spills -- measured no faster:
+// spiral27 21.6 ms either way, spiral47 23.0 -> 23.7 ms.)
+template <int POLICY, class CODE, bool SIGNAL>
 __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     constexpr int R = CODE::R;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -288,7 +305,10 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     if (blockIdx.x == 0) {   // phase of every decision row this launch writes (read by chainback)
         for (int t = threadIdx.x; t < a.nsteps; t += blockDim.x) a.row_phase[a.step0 + t] = (uint8_t)(t % NB);
     }
-    if (idx >= a.count) return;
+    if (idx >= a.count) {
+        if (SIGNAL) signal_done(a.done);
+        return;
+    }
 
     // ---- load canonical metrics into the phase-0 layout: register i = states (2i, 2i+1) ----
     uint32_t w[NW];
@@ -382,6 +402,8 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
         if (rem > 4) { run_step<POLICY, CODE, 4>(w, tb, a, off, &d); drow[4 * dstride] = d; }
     }
 
+    if (SIGNAL) signal_done(a.done);
+
     // ---- store canonical metrics: logical state n sits at physical_of(rem, n) ----
     uint32_t tmp[NW];
 #pragma unroll
@@ -399,7 +421,8 @@ template <int POLICY, class CODE>
 static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
     const int threads = 128;
     const int blocks = (a.count + threads - 1) / threads;
-    acs_k7_kernel<POLICY, CODE><<<blocks, threads, 0, st>>>(a);
+    if (a.done) acs_k7_kernel<POLICY, CODE, true><<<blocks, threads, 0, st>>>(a);
+    else acs_k7_kernel<POLICY, CODE, false><<<blocks, threads, 0, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -452,9 +475,10 @@ bool k7_supported(const CodecParams& c) {
 
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st) {
+                          int frame0, int count, cudaStream_t st, unsigned* done) {
     if (count <= 0 || nsteps <= 0) return cudaSuccess;
     k7::K7Args a;
+    a.done = done;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;

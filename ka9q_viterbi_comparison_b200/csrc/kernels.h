@@ -41,7 +41,7 @@ cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecPara
 bool k7_supported(const CodecParams& c);
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st);
+                          int frame0, int count, cudaStream_t st, unsigned* done = nullptr);
 
 // ---- group kernels for K=9 / K=15 (acs_grp.cu): decisions as one u64 per (row, frame, thread of the frame) ----
 bool grp_supported(const CodecParams& c);
