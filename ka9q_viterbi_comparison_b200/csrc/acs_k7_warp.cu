@@ -131,11 +131,118 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
     gm[lane + 32] = (uint16_t)hi;
 }
 
+// ---- K=9: the same design with 8 states (4 butterflies) per lane --------------------------------------------
+// Lane l holds old[l + 32 i], i = 0..7: butterfly j = l + 32 b (b = 0..3) finds both inputs, old[j] (slot b) and
+// old[j + 128] (slot b + 4), in its own lane. New state n = r + 32 s (lane r, slot s) comes from butterfly
+// (r >> 1) + 16 s = lane (r >> 1) + 16 (s & 1), butterfly slot s >> 1, output r & 1: the two survivors of a butterfly
+// travel as one packed u16x2 word, so a step costs 8 shuffles. The eight ballots of a step are the generic family's
+// decision row (DL_BALLOT_FRAME_MAJOR, row_words = 8): word 2b + (n & 1), bit l.
+template <int POLICY, int RT>
+__global__ void __launch_bounds__(128) acs_k9_warp_kernel(const GenericArgs a) {
+    constexpr int NBF = 4, NS = 8;
+    const int lane = threadIdx.x & 31;
+    const int fidx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (fidx >= a.count) return;
+    const int frame = a.frame0 + fidx;
+    const CodecParams& c = a.c;
+    const int R = RT ? RT : c.R;
+    constexpr int SYMB = (POLICY == P_WY_U16) ? 2 : 1;
+    constexpr int WPS = RT ? (RT * SYMB + 3) / 4 : (MAX_R * SYMB + 3) / 4;
+    const int step_bytes = R * SYMB;
+    uint16_t* gm = a.metrics + (size_t)frame * 256;
+    int m[NS];
+    unsigned cw[NBF];
+#pragma unroll
+    for (int i = 0; i < NS; i++) m[i] = gm[lane + 32 * i];
+#pragma unroll
+    for (int b = 0; b < NBF; b++) cw[b] = a.cw[lane + 32 * b];
+    const unsigned char* sp = (const unsigned char*)a.syms + (size_t)frame * a.sym_stride;
+    uint32_t* drow = a.dec + ((size_t)frame * a.dec_rows + a.step0) * 8;
+    const int srcA = lane >> 1, srcB = 16 + (lane >> 1);
+    const bool odd = lane & 1;
+
+    auto fetch = [&](uint32_t (&buf)[WPS], int t0) {
+        const int t = t0 + lane;
+#pragma unroll
+        for (int w = 0; w < WPS; w++) buf[w] = 0;
+        if (t < a.nsteps) {
+            const unsigned char* p = sp + (size_t)t * step_bytes;
+#pragma unroll
+            for (int j = 0; j < WPS * 4; j++)
+                if (j < step_bytes) buf[j >> 2] |= (uint32_t)__ldg(p + j) << ((j & 3) * 8);
+        }
+    };
+    uint32_t cur[WPS], nxt[WPS];
+    fetch(cur, 0);
+    for (int t0 = 0; t0 < a.nsteps; t0 += 32) {
+        fetch(nxt, t0 + 32);
+        const int nhere = min(32, a.nsteps - t0);
+        for (int i = 0; i < nhere; i++) {
+            uint32_t sw[WPS];
+#pragma unroll
+            for (int w = 0; w < WPS; w++) sw[w] = __shfl_sync(0xffffffffu, cur[w], i);
+            int sym[RT ? RT : MAX_R];
+#pragma unroll
+            for (int r = 0; r < (RT ? RT : MAX_R); r++) {
+                if (r < R) {
+                    const int bpos = r * SYMB;
+                    const uint32_t v = sw[bpos >> 2] >> ((bpos & 3) * 8);
+                    sym[r] = (POLICY == P_WY_U16) ? (int)(int16_t)(v & 0xffffu)
+                           : (POLICY == P_WY_U8) ? (int)(int8_t)(v & 0xffu) : (int)(v & 0xffu);
+                }
+            }
+            uint32_t pk[NBF], row[2 * NBF];
+#pragma unroll
+            for (int b = 0; b < NBF; b++) {
+                const int bm = branch_metric_rt<POLICY, RT>(c, cw[b], sym);
+                int v0, v1, d0, d1;
+                acs<POLICY>(c.max_error, m[b], m[b + NBF], bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
+                row[2 * b] = __ballot_sync(0xffffffffu, d0);
+                row[2 * b + 1] = __ballot_sync(0xffffffffu, d1);
+                pk[b] = ((uint32_t)v0 & 0xffffu) | ((uint32_t)v1 << 16);
+            }
+#pragma unroll
+            for (int s = 0; s < NS; s++) {
+                const uint32_t t = __shfl_sync(0xffffffffu, pk[s >> 1], (s & 1) ? srcB : srcA);
+                m[s] = (int)(odd ? (t >> 16) : (t & 0xffffu));
+            }
+            if (lane == 0) {
+                uint4* d = reinterpret_cast<uint4*>(drow + 8 * (size_t)(t0 + i));
+                d[0] = make_uint4(row[0], row[1], row[2], row[3]);
+                d[1] = make_uint4(row[4], row[5], row[6], row[7]);
+            }
+            if (PolicyTraits<POLICY>::has_renorm) {
+                const int m0 = __shfl_sync(0xffffffffu, m[0], 0);
+                if (renorm_needed<POLICY>(c, m0)) {                     // uniform over the warp
+                    int lm = m[0];
+#pragma unroll
+                    for (int s = 1; s < NS; s++) lm = min(lm, m[s]);
+                    const int mn = __reduce_min_sync(0xffffffffu, lm);
+#pragma unroll
+                    for (int s = 0; s < NS; s++) m[s] = renorm_apply<POLICY>(m[s], mn);
+                }
+            }
+        }
+#pragma unroll
+        for (int w = 0; w < WPS; w++) cur[w] = nxt[w];
+    }
+#pragma unroll
+    for (int i = 0; i < NS; i++) gm[lane + 32 * i] = (uint16_t)m[i];
+}
+
 template <int POLICY>
 cudaError_t launch_policy(const GenericArgs& a, cudaStream_t st) {
     const int warps_per_block = 4;
     const int blocks = (a.count + warps_per_block - 1) / warps_per_block;
     const dim3 g(blocks), b(warps_per_block * 32);
+    if (a.c.K == 9) {
+        switch (a.c.R) {
+        case 2: acs_k9_warp_kernel<POLICY, 2><<<g, b, 0, st>>>(a); break;
+        case 4: acs_k9_warp_kernel<POLICY, 4><<<g, b, 0, st>>>(a); break;
+        default: acs_k9_warp_kernel<POLICY, 0><<<g, b, 0, st>>>(a); break;
+        }
+        return cudaGetLastError();
+    }
     switch (a.c.R) {
     case 2: acs_k7_warp_kernel<POLICY, 2><<<g, b, 0, st>>>(a); break;
     case 3: acs_k7_warp_kernel<POLICY, 3><<<g, b, 0, st>>>(a); break;
@@ -148,7 +255,7 @@ cudaError_t launch_policy(const GenericArgs& a, cudaStream_t st) {
 }  // namespace
 
 bool k7_warp_supported(const CodecParams& c) {
-    return c.K == 7 && c.R <= MAX_R && c.policy != P_KA9Q_S16_615 && c.policy != P_KA9Q_S16_224 && c.policy != P_SPIRAL_615;
+    return (c.K == 7 || c.K == 9) && c.R <= MAX_R && c.policy != P_KA9Q_S16_615 && c.policy != P_KA9Q_S16_224 && c.policy != P_SPIRAL_615;
 }
 
 cudaError_t launch_acs_k7_warp(const GenericArgs& a, cudaStream_t st) {

@@ -194,8 +194,10 @@ static int create_impl(b200v_batch* h, int starting_state);
 // of the register kernel (measured, 8198-step frames: 1 frame 0.58 vs 1.63 ms, 1024 frames 2.7 vs 3.6 ms including
 // the upload, equal at 4096 frames), so up to 2048 frames the warp-per-frame family is the automatic choice.
 constexpr int K7_WARP_MAX_FRAMES = 2048;
+constexpr int K9_WARP_MAX_FRAMES = 1024;   // K=9 (8 states per lane): single frame 1.06-1.55 -> 0.66-0.94 ms, still ahead at 1024 frames
 static int fallback_variant(const b200v_batch* h) {
-    if (k7_warp_supported(h->c) && (!h->has_fast || h->n_frames <= K7_WARP_MAX_FRAMES)) return 3;
+    if (k7_warp_supported(h->c) &&
+        (!h->has_fast || h->n_frames <= (h->c.K == 7 ? K7_WARP_MAX_FRAMES : K9_WARP_MAX_FRAMES))) return 3;
     return h->has_fast ? 2 : 1;
 }
 static int layout_of_variant(const b200v_batch* h, int variant) { return variant == 2 ? h->fast_layout : DL_BALLOT_FRAME_MAJOR; }

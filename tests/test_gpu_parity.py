@@ -196,7 +196,7 @@ def test_nonstandard_polynomials_and_start_state():
         T = nbytes * 8 + K - 1
         data, syms = make_batch(c, 4, nbytes, 0.7, seed=99)
         with kv.BatchDecoder(codec, T, 4, K=K, R=R, poly=poly) as dec:
-            assert dec.variant == (3 if K == 7 else 1)      # no compile-time instance: warp-per-frame / generic
+            assert dec.variant == 3      # no compile-time instance: warp-per-frame (K=7, K=9)
             dec.reset(5)
             dec.update(syms)
             out = dec.chainback(nbytes * 8, endstate=3)
@@ -424,16 +424,16 @@ def test_wy_u16_out_of_range_symbols_take_the_generic_family(name):
     T = 90 if K == 15 else 300
     nbits = T - (K - 1)
     rng = np.random.default_rng(16)
-    # K=7: batches of up to 2048 frames run on the warp-per-frame family anyway (exact for any input), so the
+    # K=7 / K=9: batches of up to 2048 / 1024 frames run on the warp-per-frame family anyway (exact for any input), so the
     # routing away from the register kernel needs a larger batch; frames 3.. repeat the first three
-    n_frames = 2051 if K == 7 else 3
+    n_frames = 2051 if K == 7 else 1027 if K == 9 else 3
     in_range = np.resize(rng.integers(-127, 128, size=(3, T * R)), (n_frames, T * R)).astype(np.int16)
     wild = rng.integers(-32768, 32768, size=(3, T * R)).astype(np.int16)
     wild[1, ::7] = -32768
     wild[2, ::5] = 32767
     wild = np.resize(wild, (n_frames, T * R)).astype(np.int16)
     with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
-        exact = 3 if K == 7 else 1     # the exact-for-any-input family: warp-per-frame for K=7, else generic
+        exact = 3 if K in (7, 9) else 1     # the exact-for-any-input family: warp-per-frame for K=7 / K=9, else generic
         for syms, expect_variant in ((in_range, 2), (wild, exact), (in_range, 2)):
             dec.reset()
             dec.update(syms)
@@ -538,7 +538,7 @@ def test_common_codes(code, width):
         refs.append((q.decisions(0, T), q.metrics(), q.chainback(nbytes * 8, 0)))
         q.close()
     with kv.BatchDecoder(kv.WY_U8 if width == 8 else kv.WY_U16, T, n_frames, K=K, R=R, poly=poly) as dec:
-        assert dec.variant == (3 if K == 7 else 2), "every common code has a specialised kernel family (small K=7 batches: warp per frame)"
+        assert dec.variant == (3 if K in (7, 9) else 2), "every common code has a specialised kernel family (small K=7 / K=9 batches: warp per frame)"
         for v in variants(dec):
             dec.reset()
             dec.set_variant(v)
