@@ -69,22 +69,35 @@ __global__ void __launch_bounds__(256) chainback_k7_kernel(const ChainbackArgs a
     unsigned reg = ((a.endstates ? a.endstates[f] : a.endstate) % 64u) << 2;
     if (a.results) a.results[f] = 0;
     unsigned n = a.nbits;
+    // ragged top (nbits not a multiple of 8): guarded, bit by bit, down to the next byte boundary
+    while (n & 7u) {
+        const unsigned row = n - 1 + (K - 1);
+        const unsigned k = rd.bit_of(rd.load(row), row, reg >> 2);
+        reg = (reg >> 1) | (k << 7);
+        n--;
+        if ((n & 7u) == 0) out[n >> 3] = (uint8_t)reg;     // the value written at the lowest n of the byte sticks
+    }
+    // whole bytes: 8 rows in flight, no guards; the table row (phase of the step that wrote the decision row) is the
+    // same for every frame, the bit position inside the 64-bit word comes from shared memory
+    const unsigned long long* base = rd.base;
+    const size_t stride = rd.stride;
     while (n > 0) {
-        const unsigned cnt = n < (unsigned)CHUNK ? n : (unsigned)CHUNK;
         unsigned long long wbuf[CHUNK];
-#pragma unroll
-        for (int i = 0; i < CHUNK; i++)
-            if ((unsigned)i < cnt) wbuf[i] = rd.load(n - 1 - i + (K - 1));
+        unsigned ph[CHUNK];
 #pragma unroll
         for (int i = 0; i < CHUNK; i++) {
-            if ((unsigned)i < cnt) {
-                const unsigned row = n - 1 - i + (K - 1);
-                const unsigned k = rd.bit_of(wbuf[i], row, reg >> 2);
-                reg = (reg >> 1) | (k << 7);
-                if (((n - 1 - i) & 7u) == 0) out[(n - 1 - i) >> 3] = (uint8_t)reg;
-            }
+            const unsigned row = n - 1 - i + (K - 1);
+            wbuf[i] = __ldg(base + (size_t)row * stride);
+            ph[i] = (unsigned)__ldg(a.row_phase + row) * k7::S;
         }
-        n -= cnt;
+#pragma unroll
+        for (int i = 0; i < CHUNK; i++) {
+            const unsigned sh = tab[ph[i] + (reg >> 2)];
+            const unsigned k = (unsigned)(wbuf[i] >> sh) & 1u;
+            reg = (reg >> 1) | (k << 7);
+        }
+        n -= CHUNK;
+        out[n >> 3] = (uint8_t)reg;
     }
 }
 
