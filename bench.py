@@ -3,10 +3,16 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--codec ka9q27] ...
 
-One "step" = init + update + chainback of one batch of frames (BASELINE.json configs[1]: 1 Mi frames x
-2048 bits of K=7 r=1/2 per GPU; frames are independent, so ranks shard them with no collective: weak
-scaling). `value` is timed with inputs resident in HBM; `e2e` goes through b200v_batch_decode with host
-(pinned) buffers, copies included. Prints ONE JSON line on rank 0.
+One "step" = init + update + chainback of one batch of frames. The headline workload is BASELINE.json
+configs[1] (1 Mi frames x 2048 bits of K=7 r=1/2 per GPU); the default invocation also measures the other half of
+BASELINE.json's metric and the remaining configs as `secondary` workloads in the same JSON line: K=15 r=1/6
+(ka9q615: 8192 x 2048 bits and 2048 x 16384 bits, configs[3]) and K=9 (ka9q29, spiral49: 256 Ki x 2048 bits,
+configs[2]). Frames are independent, so ranks shard them with no collective: weak scaling. `value` is timed with
+inputs resident in HBM; `e2e` goes through b200v_batch_decode with host (pinned) buffers, copies included. Every
+workload carries the roofline of its dominant kernel (the bound that binds: integer issue for the update kernels),
+a CPU baseline (the compiled reference on the host cores) and `parity_sample`: frames spread over the whole
+benchmarked batch, last frame included, compared bit for bit with the checker outside the timed region.
+Prints ONE JSON line on rank 0.
 """
 import argparse
 import ctypes as C
@@ -24,8 +30,21 @@ sys.path.insert(0, ROOT)
 
 METRIC = "decoded Mbit/s (update+chainback)"
 UNIT = "Mbit/s"
-ISSUE_PEAK = 148 * 4 * 1.965e9      # warp-instructions/s: one issue slot per SM sub-partition and clock
-ALU_PEAK = 148 * 128 * 1.965e9      # dual-pipe integer issue peak, thread-instructions/s (measured 96-121 of 128 lanes)
+N_SM = 148
+
+# (K, R) of the fixed codecs (include/b200_viterbi.h b200v_codec): hard-coded so that the reference arm never maps the
+# product library
+CODEC_SHAPE = {"ka9q27": (7, 2), "ka9q29": (9, 2), "ka9q615": (15, 6), "ka9q224": (24, 2), "spiral27": (7, 2),
+               "spiral29": (9, 2), "spiral47": (7, 4), "spiral49": (9, 4), "spiral615": (15, 6)}
+
+# the default line: headline first, then the workloads BASELINE.json's metric / configs name beside it
+HEADLINE = {"codec": "ka9q27", "frames": 1 << 20, "frame_bits": 2048}
+SECONDARY = [
+    {"codec": "ka9q615", "frames": 8192, "frame_bits": 2048},       # the other half of the metric: K=15 r=1/6
+    {"codec": "ka9q615", "frames": 2048, "frame_bits": 16384},      # configs[3]: long frames
+    {"codec": "ka9q29", "frames": 1 << 18, "frame_bits": 2048},     # configs[2]
+    {"codec": "spiral49", "frames": 1 << 18, "frame_bits": 2048},   # configs[2]
+]
 
 
 def parse():
@@ -34,45 +53,62 @@ def parse():
     p.add_argument("--steps", type=int, default=5)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    p.add_argument("--codec", default="ka9q27")
+    p.add_argument("--codec", default=None, help="measure this codec only (default: the headline + the secondary workloads)")
     p.add_argument("--K", type=int, default=7, help="constraint length (wy_u8 / wy_u16 only)")
     p.add_argument("--R", type=int, default=2, help="code rate 1/R (wy_u8 / wy_u16 only)")
     p.add_argument("--frames", type=int, default=0, help="frames per GPU (default: 1 Mi for K<=9, 8192 for K=15)")
     p.add_argument("--frame-bits", type=int, default=2048)
-    p.add_argument("--sigma", type=float, default=0.7, help="channel noise (0 = main.cpp's noiseless symbols)")
-    p.add_argument("--variant", type=int, default=0, help="kernel family: 0 auto, 1 generic, 2 specialised")
+    p.add_argument("--sigma", type=float, default=None,
+                   help="channel noise (0 = main.cpp's noiseless symbols; default 0.7 for K <= 9, 1.0 above: SURVEY 8d)")
+    p.add_argument("--variant", type=int, default=0, help="kernel family: 0 auto, 1 generic, 2 specialised, 3 warp per frame")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-secondary", action="store_true")
     p.add_argument("--unfused", action="store_true", help="time init/update/chainback as three calls instead of b200v_batch_decode_dev")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-numa", action="store_true", help="do not bind the rank to the CPUs / memory node of its GPU")
     p.add_argument("--cpu-seconds", type=float, default=6.0)
+    p.add_argument("--parity-frames", type=int, default=64)
     return p.parse_args()
-
-
-# oracle registry name (CPU reference arm) for each product codec
-REF_NAME = {"ka9q27": "ka9q27", "ka9q29": "ka9q29", "ka9q615": "ka9q615", "spiral27": "spiral27",
-            "spiral29": "spiral29", "spiral47": "spiral47", "spiral49": "spiral49", "spiral615": "spiral615",
-            "ka9q224": "ka9q224"}
 
 
 def codec_shape(codec, K=7, R=2):
     """(K, R) of a fixed codec; the williamyang families take them from --K / --R."""
-    import ka9q_viterbi_comparison_b200 as kv
-    k, r = C.c_int(), C.c_int()
-    kv.load_library().b200v_codec_shape(kv.CODEC_BY_NAME[codec], C.byref(k), C.byref(r))
-    return (k.value, r.value) if k.value else (K, R)
+    return CODEC_SHAPE.get(codec, (K, R))
 
 
 def ref_name(codec, K, R):
-    """oracle registry name of the reference decoder that matches a product codec"""
+    """registry name (oracle/ref_shims/registry.cpp) of the reference decoder that matches a product codec"""
     if codec == "wy_u8":
         return f"wy_avx_u8_k{K}r{R}"
     if codec == "wy_u16":
         return f"wy_avx_u16_k{K}r{R}"
-    return REF_NAME[codec]
+    return codec
 
 
 def default_frames(K):
     return 1 << 20 if K <= 9 else 8192 if K <= 16 else 16
+
+
+def default_sigma(K):
+    return 0.7 if K <= 9 else 1.0
+
+
+def workload_text(w):
+    return f"{w['codec']} K={w['K']} r=1/{w['R']}: {w['frames']} frames x {w['frame_bits']} bits per GPU"
+
+
+def resolve_workloads(args):
+    """[headline, secondary...] as fully specified dicts (codec, K, R, frames, frame_bits, sigma)."""
+    def full(w):
+        K, R = codec_shape(w["codec"], args.K, args.R)
+        w = dict(w, K=K, R=R)
+        w.setdefault("sigma", args.sigma if args.sigma is not None else default_sigma(K))
+        return w
+    if args.codec is None and not args.frames and args.frame_bits == 2048:
+        return [full(dict(HEADLINE))] + ([] if args.no_secondary else [full(dict(s)) for s in SECONDARY])
+    codec = args.codec or "ka9q27"
+    K, _ = codec_shape(codec, args.K, args.R)
+    return [full({"codec": codec, "frames": args.frames or default_frames(K), "frame_bits": args.frame_bits})]
 
 
 def channel_params(lo, hi, sigma):
@@ -100,7 +136,7 @@ class ClockSampler:
                 self.samples.append([x.strip() for x in out.strip().split(",")])
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.05)
 
     def start(self):
         self.thread = threading.Thread(target=self._run, daemon=True)
@@ -147,18 +183,39 @@ def cpu_model():
     return f"{model}, {os.cpu_count()} threads / {len(cores) or '?'} cores"
 
 
-def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None, K=7, R=2):
-    """Decode frames of `frame_bits` with one decoder instance per host thread for ~`seconds`.
-    Returns (Mbit/s aggregate, threads, kind, sample description)."""
+def usable_cpus():
+    try:
+        return sorted(os.sched_getaffinity(0))
+    except AttributeError:
+        return list(range(os.cpu_count() or 1))
+
+
+_REF_BUILD = None
+
+
+def checker_module():
+    """tests/_oracle.py (the checker bindings); on first use selects the reference build the CPU arm times: the
+    reference preset's -march=native build when this host has every ISA flag of the host that compiled it
+    (oracle/Makefile), else the portable -march=x86-64-v3 build."""
+    global _REF_BUILD
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle as o
-    name = ref_name(codec, K, R)
+    if _REF_BUILD is None:
+        _REF_BUILD = "-O3 -ffast-math -march=native" if o.use_native_ref() else "-O3 -ffast-math -march=x86-64-v3"
+    return o
+
+
+def cpu_reference_rate(name, frame_bits, sigma, seconds, n_threads=None):
+    """Decode frames of `frame_bits` with one instance of the reference decoder `name` per host thread (each thread
+    pinned to its own CPU) for ~`seconds`. Returns (Mbit/s aggregate, threads, kind, sample description)."""
+    o = checker_module()
     c = o.codec_by_name(name)
     nbytes = frame_bits // 8
     T = frame_bits + c.K - 1
     kind = "reference" if o.ref_available() else "port"
-    n_threads = n_threads or (os.cpu_count() or 1)
-    pool = [o.make_frame(c, nbytes, sigma, seed=0xB200, frame=f)[1] for f in range(16)]
+    cpus = usable_cpus()
+    n_threads = n_threads or len(cpus)
+    pool = [o.make_frame(c, nbytes, sigma, seed=0xB200, frame=f)[1] for f in range(8 if c.K < 15 else 2)]
     # create serially: the reference's create_* fills process-global tables unguarded (SURVEY 3.5)
     decs = [(o.Ref(name, T) if kind == "reference" else o.Oracle(c, T)) for _ in range(n_threads)]
     counts = [0] * n_threads
@@ -167,6 +224,10 @@ def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None, K=7, R
     pool_arr = np.stack(pool)
 
     def work(i):
+        try:        # one CPU per thread (threads pinned); sched_setaffinity(0) acts on the calling thread
+            os.sched_setaffinity(0, {cpus[i % len(cpus)]})
+        except (AttributeError, OSError):
+            pass
         d = decs[i]
         if c_loop:      # whole loop in C (GIL released): measures the decoder, not the interpreter
             counts[i], _ = d.time_decode(pool_arr, T, frame_bits, seconds)
@@ -190,33 +251,66 @@ def cpu_reference_rate(codec, frame_bits, sigma, seconds, n_threads=None, K=7, R
         d.close()
     frames = sum(counts)
     return frames * frame_bits / dt / 1e6, n_threads, kind, \
-        f"{frames} frames x {frame_bits} bits of {name}, sigma={sigma}, {n_threads} threads, {dt:.1f} s, host {cpu_model()}"
+        f"{frames} frames x {frame_bits} bits of {name}, sigma={sigma}, {n_threads} pinned threads, {dt:.1f} s, " \
+        f"host {cpu_model()}, reference built {_REF_BUILD}"
+
+
+# the reference's other CPU decoders of the same code (ka9q, spiral, sse_u8, avx_u8, sse_u16, avx_u16):
+# the speed-up is quoted against the same-named decoder AND the fastest of these
+def cpu_family(K, R):
+    fam = {(7, 2): ["ka9q27", "spiral27"], (9, 2): ["ka9q29", "spiral29"], (7, 4): ["spiral47"], (9, 4): ["spiral49"],
+           (15, 6): ["ka9q615", "spiral615"], (24, 2): ["ka9q224"]}.get((K, R), [])
+    return fam + [f"wy_{isa}_u{w}_k{K}r{R}" for isa in ("sse", "avx") for w in (8, 16)]
+
+
+def cpu_baseline_block(w, seconds, alternatives_seconds=0.0):
+    name = ref_name(w["codec"], w["K"], w["R"])
+    v, cores, kind, sample = cpu_reference_rate(name, w["frame_bits"], w["sigma"], seconds)
+    out = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample, "decoder": name}
+    if alternatives_seconds > 0 and kind == "reference":
+        alts = {}
+        for alt in cpu_family(w["K"], w["R"]):
+            if alt == name:
+                continue
+            try:
+                alts[alt] = cpu_reference_rate(alt, w["frame_bits"], w["sigma"], alternatives_seconds)[0]
+            except Exception:
+                pass
+        best = max(list(alts.items()) + [(name, v)], key=lambda kv_: kv_[1])
+        out["other_decoders_of_this_code"] = alts
+        out["fastest"] = {"decoder": best[0], "value": best[1]}
+    return out
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    K, R = codec_shape(args.codec, args.K, args.R)
-    per_step = max(1.0, min(args.cpu_seconds, 240.0 / max(1, args.steps + args.warmup)))
-    vals = []
-    info = None
+    loads = resolve_workloads(args)
+    head = loads[0]
+    per_step = max(1.0, min(args.cpu_seconds, 200.0 / max(1, args.steps + args.warmup)))
+    vals, info = [], None
+    name = ref_name(head["codec"], head["K"], head["R"])
     for i in range(args.warmup + args.steps):
-        v, cores, kind, sample = cpu_reference_rate(args.codec, args.frame_bits, args.sigma, per_step, K=K, R=R)
+        v, cores, kind, sample = cpu_reference_rate(name, head["frame_bits"], head["sigma"], per_step)
         if i >= args.warmup:
             vals.append(v)
             info = (cores, kind, sample)
     value = float(np.mean(vals))
-    frames = args.frames or default_frames(K)
+    secondary = []
+    for w in loads[1:]:
+        cb = cpu_baseline_block(w, min(3.0, args.cpu_seconds))
+        secondary.append({"config": {"workload": workload_text(w), "sigma": w["sigma"]}, "value": cb["value"], "unit": UNIT,
+                          "cpu_baseline": cb,
+                          "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.codec} K={K} r=1/{R}: {frames} frames x {args.frame_bits} bits per GPU",
-                   "sigma": args.sigma},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": info[0], "kind": info[1], "sample": info[2]},
+        "config": {"workload": workload_text(head), "sigma": head["sigma"]},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": info[0], "kind": info[1], "sample": info[2], "decoder": name},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "secondary": secondary,
     }
     emit(line)
 
@@ -224,29 +318,94 @@ def run_reference_arm(args):
 # ---------------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------------
-def run_b200_arm(args):
+class Ranks:
+    """barrier and max-over-ranks through gloo (no NCCL: the data path has no collective)"""
+
+    def __init__(self):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("gloo")
+            self.dist = dist
+
+    def barrier(self):
+        import torch
+        torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(self, x, op="max"):
+        if self.dist is None:
+            return float(x)
+        import torch
+        t = torch.tensor([float(x)], dtype=torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def load_json(path, default):
+    try:
+        return json.load(open(path))
+    except Exception:
+        return default
+
+
+def parity_sample(w, dec, d_syms, d_out, srow, orow, T, n_sample):
+    """Bit-check of the benchmarked launch against the checker (the compiled reference where it travelled with the
+    snapshot, else the C restatement), outside the timed region: `n_sample` frames spread over the whole batch, first
+    and last included -> decoded bytes of every sampled frame, decision vectors of four of them."""
+    o = checker_module()
+    name = ref_name(w["codec"], w["K"], w["R"])
+    c = o.codec_by_name(name)
+    use_ref = o.ref_available()
+    if not use_ref and w["K"] >= 15:
+        n_sample = min(n_sample, 8)          # the scalar restatement needs ~0.2 s per 2048-bit K=15 frame
+    if w["K"] >= 15:
+        n_sample = min(n_sample, 16 if w["frame_bits"] <= 2048 else 6)
+    if w["K"] > 16:
+        n_sample = min(n_sample, 2)
+    frames, nbits = w["frames"], w["frame_bits"]
+    idx = sorted(set(int(round(x)) for x in np.linspace(0, frames - 1, min(n_sample, frames))))
+    with_decisions = set(idx[:: max(1, len(idx) // 3)][:3] + [idx[-1]])
+    chk = o.Ref(name, T) if use_ref else o.Oracle(c, T)
+    sdt = o.sym_dtype(c)
+    mism, dec_mism = 0, 0
+    for f in idx:
+        syms = d_syms[f * srow:(f + 1) * srow].cpu().numpy().view(sdt)
+        got = d_out[f * orow:(f + 1) * orow].cpu().numpy()
+        want, want_dec = chk.decode(syms, nbits)
+        if not np.array_equal(got, want[:orow]):
+            mism += 1
+        if f in with_decisions and not np.array_equal(dec.decisions(f, 0, T), want_dec):
+            dec_mism += 1
+    chk.close()
+    return {"frames": len(idx), "mismatches": mism, "decision_frames": len(with_decisions), "decision_mismatches": dec_mism,
+            "first_frame": idx[0], "last_frame": idx[-1], "checker": "reference" if use_ref else "port"}
+
+
+def measure(args, ranks, w, steps, warmup, cpu_seconds, headline):
+    """One workload on this rank's GPU: HBM-resident rate, e2e rate, roofline, parity sample, CPU baseline."""
     import torch
     import ka9q_viterbi_comparison_b200 as kv
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
+    local, rank, world = ranks.local, ranks.rank, ranks.world
     dev = torch.device("cuda", local)
-
-    codec = kv.CODEC_BY_NAME[args.codec]
-    K, R = codec_shape(args.codec, args.K, args.R)
+    lib = kv.load_library()
+    codec = kv.CODEC_BY_NAME[w["codec"]]
+    K, R, frames, nbits, sigma = w["K"], w["R"], w["frames"], w["frame_bits"], w["sigma"]
     S = 1 << (K - 1)
-    nbits = args.frame_bits
     T = nbits + K - 1
-    frames = args.frames or default_frames(K)
-    sym_bytes = kv.load_library().b200v_codec_symbol_bytes(codec)
-    lo, hi = (-3, 3) if args.codec == "wy_u8" else {1: (0, 255)}.get(sym_bytes, (-127, 127))
+    sym_bytes = lib.b200v_codec_symbol_bytes(codec)
+    lo, hi = (-3, 3) if w["codec"] == "wy_u8" else {1: (0, 255)}.get(sym_bytes, (-127, 127))
     srow, orow = T * R * sym_bytes, nbits // 8
 
     dec = kv.BatchDecoder(codec, T, frames, K=K, R=R, device=local)
@@ -261,7 +420,7 @@ def run_b200_arm(args):
     d_syms = torch.empty(frames * srow, dtype=torch.uint8, device=dev)
     d_data = torch.empty(frames * orow, dtype=torch.uint8, device=dev)
     d_out = torch.empty(frames * orow, dtype=torch.uint8, device=dev)
-    amp_q8, sigma_q8, mean_q8, lo, hi = channel_params(lo, hi, args.sigma)
+    amp_q8, sigma_q8, mean_q8, lo, hi = channel_params(lo, hi, sigma)
     dec.generate_dev(d_syms, srow, d_data, orow, nbits, 0xB200, rank * frames, amp_q8, sigma_q8, mean_q8, lo, hi)
     torch.cuda.synchronize()
 
@@ -276,133 +435,175 @@ def run_b200_arm(args):
         else:
             dec.decode_dev(d_syms, srow, d_out, orow, nbits)
 
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
-    barrier()
+    ranks.barrier()
     launches0 = dec.launch_count
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    upd_ms, cb_ms = [], []
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step()
     e1.record()
-    barrier()
-    total_ms = e0.elapsed_time(e1)
+    ranks.barrier()
+    total_ms = ranks.reduce(e0.elapsed_time(e1))
     launches = dec.launch_count - launches0
     # per-kernel device time (CUDA events on the launching stream, recorded inside the library)
+    upd_ms, cb_ms = [], []
     for _ in range(3):
         step_calls()
         u, c = dec.last_kernel_ms()
         upd_ms.append(u)
         cb_ms.append(c)
     clocks = sampler.stop() if rank == 0 else None
-
-    # correctness guard inside the bench: decoded output vs generated data
-    err_bits = int(np.unpackbits(torch.bitwise_xor(d_out[: 4096 * orow], d_data[: 4096 * orow]).cpu().numpy()).sum())
-    ber = err_bits / float(4096 * nbits)
-
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
+    ms_per_step = total_ms / steps
     value = world * frames * nbits / (ms_per_step * 1e-3) / 1e6
+
+    # correctness guards, outside the timed region: BER against the generated data, then the bit-check against the checker
+    n_ber = min(frames, 4096)
+    err_bits = int(np.unpackbits(torch.bitwise_xor(d_out[: n_ber * orow], d_data[: n_ber * orow]).cpu().numpy()).sum())
+    ber = err_bits / float(n_ber * nbits)
+    ber_limit = 0.0 if sigma == 0 else 0.02
+    parity = parity_sample(w, dec, d_syms, d_out, srow, orow, T, args.parity_frames)
+    parity["mismatches"] = int(ranks.reduce(parity["mismatches"], "sum"))
+    parity["decision_mismatches"] = int(ranks.reduce(parity["decision_mismatches"], "sum"))
+    parity["frames"] *= world
+    rejected = []
+    if ber > ber_limit:
+        rejected.append(f"sample BER {ber:.3g} above {ber_limit}")
+    if parity["mismatches"] or parity["decision_mismatches"]:
+        rejected.append("parity sample differs from the checker")
 
     # ---- end-to-end through the C-ABI batch entry point with host buffers ----
     e2e = None
     if not args.no_e2e:
-        lib = kv.load_library()
         h_syms = lib.b200v_host_alloc_pinned(frames * srow)
         h_out = lib.b200v_host_alloc_pinned(frames * orow)
         if not h_syms or not h_out:
             raise RuntimeError("pinned allocation failed")
         lib.b200v_memcpy_d2h(local, h_syms, d_syms.data_ptr(), frames * srow)
-        e2e_steps = max(1, min(args.steps, 3))
-        for _ in range(1):
-            rc = lib.b200v_batch_decode(dec.h, h_syms, h_out, nbits)
-            assert rc == 0, lib.b200v_last_error()
-        barrier()
+        e2e_steps = max(1, min(steps, 3))
+        rc = lib.b200v_batch_decode(dec.h, h_syms, h_out, nbits)
+        assert rc == 0, lib.b200v_last_error()
+        ranks.barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             rc = lib.b200v_batch_decode(dec.h, h_syms, h_out, nbits)
             assert rc == 0, lib.b200v_last_error()
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if dist is not None:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dt = float(tt.item())
+        dt = ranks.reduce(time.perf_counter() - t0)
+        # the host-buffer path must produce the same bytes as the device path did
+        h_view = np.ctypeslib.as_array(C.cast(h_out, C.POINTER(C.c_uint8)), shape=(frames * orow,))
+        tail = slice((frames - min(frames, 256)) * orow, frames * orow)
+        if not np.array_equal(h_view[tail], d_out[tail].cpu().numpy()):
+            rejected.append("e2e output differs from the device-path output")
         e2e = {"value": world * frames * nbits * e2e_steps / dt / 1e6, "unit": UNIT,
-               "h2d_bytes_per_step": frames * srow, "d2h_bytes_per_step": frames * orow, "steps": e2e_steps}
+               "h2d_bytes_per_step": frames * srow, "d2h_bytes_per_step": frames * orow, "steps": e2e_steps,
+               "h2d_gbs": world * frames * srow * e2e_steps / dt / 1e9}
         lib.b200v_host_free_pinned(h_syms)
         lib.b200v_host_free_pinned(h_out)
 
+    variant = dec.variant
+    del d_syms, d_data, d_out
+    dec.close()
+    torch.cuda.empty_cache()
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
+        return None
 
-    # ---- roofline of the dominant kernel (update): algorithmic bytes = symbols in + decision bits out ----
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
+    # ---- roofline of the dominant kernel (update). The bound that binds is integer issue: SURVEY 8d's
+    # 4*S lane-ops per trellis step against SMs x 128 lanes/clk x f x pack (pack = 2: u16x2 lanes, every policy computes
+    # in 16-bit lanes); issue_frac = executed warp-instructions per issue slot. HBM figures are kept beside it. ----
+    peaks = load_json(os.path.join(ROOT, "MEASURED_PEAKS.json"), {})
     peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
-    upd = float(np.median(upd_ms))
-    cb = float(np.median(cb_ms))
-    bytes_per_step_frame = R * sym_bytes + S / 8.0
-    achieved = frames * T * bytes_per_step_frame / (upd * 1e-3) / 1e9
-    lane_ops = frames * T * 4.0 * S                      # 4*S integer lane-ops per step
-    traffic, traffic_src, warp_inst = None, None, None
-    try:     # DRAM bytes per launch as ncu measured them (profiles/ncu_traffic.json: per frame-step, scaled to this launch)
-        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(
-            f"{args.codec}_k{K}r{R}" if args.codec.startswith("wy_") else args.codec)
-        if tr:
-            traffic, traffic_src = tr["bytes_per_frame_step"] * frames * T, tr["capture"]
-            if tr.get("warp_inst_per_frame_step"):
-                warp_inst = tr["warp_inst_per_frame_step"] * frames * T
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": frames * T * bytes_per_step_frame, "kernel": "update", "kernel_ms": upd, "chainback_ms": cb,
-                "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
-                # the roofline that actually binds the update kernels: integer issue, two pipes of 64 lanes
-                # per clock and SM at the measured SM clock limit (tools/ubench_int.cu, profiles/r01_ubench_int_pipes.jsonl)
-                "alu": {"lane_ops_per_s": lane_ops / (upd * 1e-3), "peak_lane_ops_per_s": ALU_PEAK,
-                        "frac": lane_ops / (upd * 1e-3) / ALU_PEAK,
-                        # executed warp-instructions (ncu count of the same kernel, scaled to this launch) per issue slot
-                        "issue_frac": (warp_inst / (upd * 1e-3) / ISSUE_PEAK) if warp_inst else None,
-                        "note": "frac: 4*S scalar lane-ops per trellis step (SURVEY 8d) vs 148 SMs x 128 thread-instructions/clk "
-                                "x 1.965 GHz -- packed u16x2 instructions carry two lanes, so frac can exceed 1; issue_frac: "
-                                "warp-instructions ncu counted for this kernel / (148 x 4 issue slots x 1.965 GHz x kernel time)"}}
-
+    f_hz = float(peaks.get("sm_max_mhz", 1965.0)) * 1e6
+    upd, cb = float(np.median(upd_ms)), float(np.median(cb_ms))
+    units = frames * T                                      # frame-steps per launch
+    bytes_per_unit = R * sym_bytes + S / 8.0                # update kernel: symbols in + decision bits out
+    lane_ops = units * 4.0 * S
+    pack = 2
+    peak_lane = N_SM * 128 * f_hz * pack
+    key = f"{w['codec']}_k{K}r{R}" if w["codec"].startswith("wy_") else w["codec"]
+    tr = load_json(os.path.join(ROOT, "profiles", "ncu_traffic.json"), {}).get(key) or {}
+    traffic = tr["bytes_per_frame_step"] * units if tr.get("bytes_per_frame_step") else None
+    warp_inst = tr["warp_inst_per_frame_step"] * units if tr.get("warp_inst_per_frame_step") else None
+    hbm_achieved = units * bytes_per_unit / (upd * 1e-3) / 1e9
+    cb_bytes = units * (4 + 1.0 / 8) if K <= 7 else units * (4 + 1.0 / 8)       # one 32-bit word per step + output
+    roofline = {
+        "bound": "int-issue", "kernel": "update", "kernel_ms": upd, "share_of_step": upd / (upd + cb) if upd + cb > 0 else None,
+        "achieved": lane_ops / (upd * 1e-3) / 1e12, "peak": peak_lane / 1e12, "unit": "Tlane-op/s", "frac": lane_ops / (upd * 1e-3) / peak_lane,
+        "pack": pack, "lane_ops_per_unit": 4 * S, "units_per_launch": units,
+        "issue_frac": (warp_inst / (upd * 1e-3) / (N_SM * 4 * f_hz)) if warp_inst else None,
+        "warp_inst_per_unit": tr.get("warp_inst_per_frame_step"), "traffic": traffic, "traffic_source": tr.get("capture"),
+        "peak_source": ("MEASURED_PEAKS.json sm_max_mhz" if peaks else "fallback 1965 MHz") + " x 148 SMs x 128 lanes/clk x pack 2",
+        "hbm": {"achieved": hbm_achieved, "peak": peak_gbs, "unit": "GB/s", "frac": hbm_achieved / peak_gbs,
+                "algorithmic_bytes": units * bytes_per_unit, "bytes_per_unit": bytes_per_unit,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
+        "chainback": {"kernel_ms": cb, "bound": "hbm", "achieved": cb_bytes / (cb * 1e-3) / 1e9 if cb > 0 else None,
+                      "peak": peak_gbs, "unit": "GB/s", "frac": cb_bytes / (cb * 1e-3) / 1e9 / peak_gbs if cb > 0 else None,
+                      "algorithmic_bytes": cb_bytes},
+    }
     cpu = None
     if not args.no_cpu_baseline:
-        v, cores, kind, sample = cpu_reference_rate(args.codec, nbits, args.sigma, args.cpu_seconds, K=K, R=R)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
-
-    line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8" if sym_bytes == 1 else "u16", "data": "synthetic",
-        "config": {"workload": f"{args.codec} K={K} r=1/{R}: {frames} frames x {nbits} bits per GPU",
-                   "sigma": args.sigma, "kernel_variant": dec.variant, "entry": "calls" if args.unfused else "decode_dev", "l2": "inputs larger than L2"
-                   if frames * srow > 126e6 else "inputs smaller than L2", "sample_ber": ber},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        cpu = cpu_baseline_block(w, cpu_seconds, alternatives_seconds=1.5 if headline else 0.0)
+    out = {
+        "config": {"workload": workload_text(w), "sigma": sigma},
+        "value": value, "unit": UNIT, "ms_per_step": ms_per_step, "steps": steps, "warmup": warmup,
+        "dtype": "u8" if sym_bytes == 1 else "u16", "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        "cpu_baseline": cpu, "parity_sample": parity, "clocks": clocks,
+        "detail": {"kernel_variant": variant, "entry": "calls" if args.unfused else "decode_dev",
+                   "l2": "inputs larger than L2" if frames * srow > 126e6 else "inputs smaller than L2: 256 MiB L2 flush not needed, "
+                         "every step rewrites the decision buffer (> L2)" if frames * T * S / 8 > 126e6 else "inputs smaller than L2",
+                   "sample_ber": ber},
     }
-    emit(line)
-    if dist is not None:
-        dist.destroy_process_group()
+    if rejected:
+        out["rejected"] = rejected
+    return out
+
+
+def bind_near_gpu(local, enable):
+    """Bind this rank (CPUs + preferred memory node) to the NUMA node of its GPU before anything allocates pinned memory."""
+    if not enable:
+        return None
+    try:
+        import ka9q_viterbi_comparison_b200 as kv
+        lib = kv.load_library()
+        if not hasattr(lib, "b200v_bind_host_to_device"):
+            return None
+        node = lib.b200v_bind_host_to_device(local)
+        return int(node)
+    except Exception:
+        return None
+
+
+def run_b200_arm(args):
+    import torch
+    ranks = Ranks()
+    numa = bind_near_gpu(ranks.local, not args.no_numa)
+    torch.cuda.set_device(ranks.local)
+    loads = resolve_workloads(args)
+    results = []
+    for i, w in enumerate(loads):
+        head = i == 0
+        res = measure(args, ranks, w, args.steps if head else max(1, min(args.steps, 5)), max(args.warmup, 3),
+                      args.cpu_seconds if head else min(3.0, args.cpu_seconds), head)
+        results.append(res)
+    if ranks.rank == 0:
+        h = results[0]
+        line = {
+            "metric": METRIC, "value": h["value"], "unit": UNIT, "n_gpus": ranks.world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": h["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": h["dtype"], "data": "synthetic", "config": h["config"], "clocks": h["clocks"],
+            "e2e": h["e2e"], "gpu_launches": sum(r["gpu_launches"] for r in results), "roofline": h["roofline"],
+            "cpu_baseline": h["cpu_baseline"], "parity_sample": h["parity_sample"], "detail": dict(h["detail"], numa_node=numa),
+            "secondary": results[1:],
+        }
+        rej = [f"{r['config']['workload']}: {x}" for r in results for x in r.get("rejected", [])]
+        if rej:
+            line["rejected"] = rej
+        emit(line)
+    ranks.close()
 
 
 _JSON_OUT = None
@@ -416,8 +617,7 @@ def emit(line):
 def main():
     global _JSON_OUT
     args = parse()
-    # libraries print to stdout behind our back (NCCL: "NCCL version ..." at communicator creation): everything but
-    # the JSON line goes to stderr
+    # libraries print to stdout behind our back: everything but the JSON line goes to stderr
     sys.stdout.flush()
     _JSON_OUT = os.dup(1)
     os.dup2(2, 1)

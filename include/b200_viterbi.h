@@ -210,11 +210,22 @@ int b200v_sharded_shard(const b200v_sharded* s, int shard, int* frame0, int* cou
 int b200v_sharded_decode(b200v_sharded* s, const void* syms, uint8_t* data, unsigned nbits);
 const char* b200v_sharded_last_error(const b200v_sharded* s);
 
+/* Bind the calling host thread (and what it allocates from now on, pinned buffers included) to the CPUs and the memory
+ * node of `device`'s PCIe root complex (sysfs topology; sched_setaffinity + set_mempolicy(MPOL_PREFERRED)). The
+ * host-buffer path is PCIe-bound end to end, so where the staging memory lives decides the multi-GPU rate: call it
+ * once per rank / shard thread BEFORE b200v_host_alloc_pinned. Returns the node (>= 0), or -1 if the topology is not
+ * exposed (nothing changed). b200v_sharded_decode's shard threads call it themselves. */
+int b200v_bind_host_to_device(int device);
+
 /* ---- device / pinned-host memory helpers (so a C host needs nothing but this library) ---- */
 void* b200v_device_alloc(int device, size_t bytes);
 void  b200v_device_free(int device, void* p);
 void* b200v_host_alloc_pinned(size_t bytes);
 void  b200v_host_free_pinned(void* p);
+/* 1 if p is page-locked host memory known to CUDA (b200v_host_alloc_pinned, cudaMallocHost, cudaHostRegister), else 0.
+ * b200v_batch_decode / b200v_sharded_decode accept pageable buffers, but the driver then stages every chunk copy
+ * synchronously: copies stop overlapping the kernels and the end-to-end rate drops to the staging rate. */
+int   b200v_host_is_pinned(const void* p);
 int   b200v_memcpy_h2d(int device, void* dst, const void* src, size_t bytes);
 int   b200v_memcpy_d2h(int device, void* dst, const void* src, size_t bytes);
 

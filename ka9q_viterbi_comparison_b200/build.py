@@ -76,17 +76,34 @@ def build_library(force=False, verbose=False):
             raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
         if res is not None and verbose:
             print(res.stderr)
-    res = subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] +
+    tmp = LIB_PATH + f".tmp{os.getpid()}"          # link under a temporary name: a concurrent dlopen never sees half a file
+    res = subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", tmp] +
                          [obj for obj, _ in results], capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc link failed:\n" + res.stdout + res.stderr)
+    os.replace(tmp, LIB_PATH)
     cxx = shutil.which("g++") or "g++"
-    res = subprocess.run([cxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-I", INCLUDE_DIR, "-o", COMPAT_LIB_PATH,
+    tmp = COMPAT_LIB_PATH + f".tmp{os.getpid()}"
+    res = subprocess.run([cxx, "-std=c++17", "-O2", "-fPIC", "-shared", "-I", INCLUDE_DIR, "-o", tmp,
                           COMPAT_SRC, "-L", PKG_DIR, "-lb200viterbi", "-Wl,-rpath,$ORIGIN"],
                          capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("building libb200viterbi_compat.so failed:\n" + res.stdout + res.stderr)
+    os.replace(tmp, COMPAT_LIB_PATH)
     return LIB_PATH
+
+
+def build_library_locked(force=False, verbose=False):
+    """build_library under an inter-process lock: the ranks of a multi-GPU run start together, and only one of them may
+    run nvcc into the shared object directory; the others wait and then find the library up to date."""
+    import fcntl
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    with open(os.path.join(OBJ_DIR, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            return build_library(force=force, verbose=verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
 
 
 if __name__ == "__main__":

@@ -593,19 +593,31 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
     const int chunk = (((h->n_frames + nchunks - 1) / nchunks) + 127) / 128 * 128;
     for (int i = 0; i < b200v_batch::NPIPE; i++) CUDA_TRY(cudaStreamWaitEvent(h->pipe[i], h->ev_pipe, 0));
     int k = 0;
-    for (int f0 = 0; f0 < h->n_frames; f0 += chunk, k++) {
+    rc = B200V_OK;
+    cudaError_t ce = cudaSuccess;
+    for (int f0 = 0; f0 < h->n_frames && rc == B200V_OK && ce == cudaSuccess; f0 += chunk, k++) {
         const int cnt = (h->n_frames - f0 < chunk) ? h->n_frames - f0 : chunk;
         cudaStream_t st = h->pipe[k % b200v_batch::NPIPE];
-        CUDA_TRY(cudaMemcpyAsync((char*)h->d_syms_stage + (size_t)f0 * srow, (const char*)syms + (size_t)f0 * srow,
-                                 (size_t)cnt * srow, cudaMemcpyHostToDevice, st));
+        ce = cudaMemcpyAsync((char*)h->d_syms_stage + (size_t)f0 * srow, (const char*)syms + (size_t)f0 * srow,
+                             (size_t)cnt * srow, cudaMemcpyHostToDevice, st);
+        if (ce != cudaSuccess) break;
         rc = launch_update_range(h, h->d_syms_stage, srow, nsteps, 0, f0, cnt, st);
-        if (rc) return rc;
+        if (rc) break;
         rc = launch_chainback_range(h, h->d_out_stage, orow, nbits, 0, f0, cnt, st, nullptr, true);
-        if (rc) return rc;
-        CUDA_TRY(cudaMemcpyAsync(data + (size_t)f0 * orow, h->d_out_stage + (size_t)f0 * orow, (size_t)cnt * orow,
-                                 cudaMemcpyDeviceToHost, st));
+        if (rc) break;
+        ce = cudaMemcpyAsync(data + (size_t)f0 * orow, h->d_out_stage + (size_t)f0 * orow, (size_t)cnt * orow,
+                             cudaMemcpyDeviceToHost, st);
     }
-    for (int i = 0; i < b200v_batch::NPIPE; i++) CUDA_TRY(cudaStreamSynchronize(h->pipe[i]));
+    // success or not, nothing of this call may still be running on the pipeline streams when it returns: the caller
+    // owns `syms` and `data` again
+    for (int i = 0; i < b200v_batch::NPIPE; i++) {
+        const cudaError_t se = cudaStreamSynchronize(h->pipe[i]);
+        if (ce == cudaSuccess) ce = se;
+    }
+    if (rc) return rc;
+    if (ce != cudaSuccess)
+        return fail(ce == cudaErrorMemoryAllocation ? B200V_ERR_NOMEM : B200V_ERR_CUDA, "pipelined decode failed: %s",
+                    cudaGetErrorString(ce));
     h->cursor = nsteps;
     return B200V_OK;
 }
@@ -825,6 +837,11 @@ extern "C" void* b200v_host_alloc_pinned(size_t bytes) {
     return p;
 }
 extern "C" void b200v_host_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+extern "C" int b200v_host_is_pinned(const void* p) {
+    cudaPointerAttributes at;
+    if (!p || cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return at.type == cudaMemoryTypeHost ? 1 : 0;
+}
 extern "C" int b200v_memcpy_h2d(int device, void* dst, const void* src, size_t bytes) {
     CUDA_TRY(cudaSetDevice(device));
     CUDA_TRY(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));

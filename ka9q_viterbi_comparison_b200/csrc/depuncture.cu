@@ -13,10 +13,12 @@ namespace {
 
 template <typename T>
 __global__ void depuncture_kernel(const DepunctureArgs a) {
-    const int frame = blockIdx.y;
+    // frames on grid.x (2^31 - 1 blocks), the symbol blocks of a frame on grid.y (<= 64): gridDim.y is capped at 65535,
+    // and the headline batch has 1 Mi frames
+    const int frame = blockIdx.x;
     const T* in = reinterpret_cast<const T*>((const unsigned char*)a.in + (size_t)frame * a.in_stride) + a.in_offset;
     T* out = reinterpret_cast<T*>((unsigned char*)a.out + (size_t)frame * a.out_stride) + a.out_offset;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < a.n_out; k += gridDim.x * blockDim.x) {
+    for (int k = blockIdx.y * blockDim.x + threadIdx.x; k < a.n_out; k += gridDim.y * blockDim.x) {
         const int q = k / a.code_len, j = k - q * a.code_len;
         const bool kept = a.prefix[j + 1] != a.prefix[j];
         out[k] = kept ? in[(size_t)q * a.prefix[a.code_len] + a.prefix[j]] : (T)a.fill;
@@ -29,7 +31,7 @@ cudaError_t launch_depuncture(const DepunctureArgs& a, int sym_bytes, int n_fram
     if (n_frames <= 0 || a.n_out <= 0) return cudaSuccess;
     int bx = (a.n_out + 255) / 256;
     if (bx > 64) bx = 64;
-    const dim3 grid((unsigned)bx, (unsigned)n_frames);
+    const dim3 grid((unsigned)n_frames, (unsigned)bx);
     if (sym_bytes == 2) depuncture_kernel<int16_t><<<grid, 256, 0, st>>>(a);
     else depuncture_kernel<uint8_t><<<grid, 256, 0, st>>>(a);
     return cudaGetLastError();

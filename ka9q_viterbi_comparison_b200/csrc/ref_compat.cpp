@@ -4,6 +4,7 @@
 #include "../../include/ref_compat/b200_ref_compat.h"
 #include "../../include/b200_viterbi.h"
 
+#include <cstdio>
 #include <cstdlib>
 
 static int g_device = -1;
@@ -21,24 +22,31 @@ static int compat_device() {
 struct CompatInstance {
     b200v_batch* h;
     int R;
+    bool failed;        // an update failed: the reference's update is void, so the failure surfaces at the next chainback
 };
 
 static CompatInstance* compat_create(int codec, int K, int R, const int* poly, int len) {
     b200v_batch* h = b200v_batch_create(codec, K, R, poly, len, 1, compat_device(), nullptr);
     if (!h) return nullptr;
-    return new CompatInstance{ h, R };
+    return new CompatInstance{ h, R, false };
 }
 static int compat_init(CompatInstance* p, int starting_state) {
     if (!p) return -1;
+    p->failed = false;
     if (b200v_batch_init(p->h, starting_state) != B200V_OK) return -1;
     return b200v_batch_sync(p->h) == B200V_OK ? 0 : -1;       // callers time each call on the host
 }
 static void compat_update(CompatInstance* p, unsigned char* syms, int nbits) {
     if (!p || nbits <= 0) return;
-    b200v_batch_update(p->h, syms, (size_t)nbits * (size_t)p->R, nbits);
+    if (b200v_batch_update(p->h, syms, (size_t)nbits * (size_t)p->R, nbits) != B200V_OK) {
+        // the reference's signature has no error channel: say why, and make the following chainback fail instead of
+        // tracing back stale decisions
+        fprintf(stderr, "b200v compat: update of %d steps failed: %s\n", nbits, b200v_last_error());
+        p->failed = true;
+    }
 }
 static int compat_chainback(CompatInstance* p, unsigned char* data, unsigned nbits, unsigned endstate) {
-    if (!p) return -1;
+    if (!p || p->failed) return -1;
     if (b200v_batch_chainback(p->h, data, (nbits + 7) / 8, nbits, endstate) != B200V_OK) return -1;
     int rc = 0;
     if (b200v_batch_chainback_results(p->h, &rc) != B200V_OK) return -1;

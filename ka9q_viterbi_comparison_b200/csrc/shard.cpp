@@ -23,7 +23,7 @@ extern "C" int b200v_shard_range(int n_frames, int n_shards, int shard, int* fra
 struct b200v_sharded {
     int n_frames = 0, frame_steps = 0, sym_row = 0;
     std::vector<b200v_batch*> inst;
-    std::vector<int> frame0, count;
+    std::vector<int> frame0, count, device;
     std::string error;
 };
 
@@ -42,7 +42,7 @@ extern "C" b200v_sharded* b200v_sharded_create(int codec, int K, int R, const in
             delete s;
             return nullptr;           // b200v_last_error() holds the reason
         }
-        s->inst.push_back(h); s->frame0.push_back(f0); s->count.push_back(cnt);
+        s->inst.push_back(h); s->frame0.push_back(f0); s->count.push_back(cnt); s->device.push_back(devices[g]);
     }
     int k = 0, r = 0;
     b200v_codec_shape(codec, &k, &r);
@@ -79,6 +79,7 @@ extern "C" int b200v_sharded_decode(b200v_sharded* s, const void* syms, uint8_t*
     for (size_t g = 0; g < n; g++) {
         if (!s->inst[g]) continue;
         th.emplace_back([&, g]() {
+            b200v_bind_host_to_device(s->device[g]);      // the thread that issues this shard's copies runs next to its GPU
             rc[g] = b200v_batch_decode(s->inst[g], (const char*)syms + (size_t)s->frame0[g] * (size_t)s->sym_row,
                                        data + (size_t)s->frame0[g] * orow, nbits);
             if (rc[g] != B200V_OK) msg[g] = b200v_last_error();      // thread-local in the library

@@ -59,7 +59,7 @@ def load_library():
         return _lib
     path = _build.LIB_PATH
     if not os.path.exists(path) or (_build.nvcc_path() and _build.needs_build()):
-        _build.build_library()
+        _build.build_library_locked()
     if not os.path.exists(path):
         raise B200ViterbiError(f"{path} is missing and cannot be built: the CUDA extension is required")
     lib = C.CDLL(path)
@@ -101,10 +101,12 @@ def load_library():
         "b200v_sharded_shard": (i32, [vp, i32, C.POINTER(i32), C.POINTER(i32)]),
         "b200v_sharded_decode": (i32, [vp, vp, vp, u32]),
         "b200v_sharded_last_error": (C.c_char_p, [vp]),
+        "b200v_bind_host_to_device": (i32, [i32]),
         "b200v_device_alloc": (vp, [i32, sz]),
         "b200v_device_free": (None, [i32, vp]),
         "b200v_host_alloc_pinned": (vp, [sz]),
         "b200v_host_free_pinned": (None, [vp]),
+        "b200v_host_is_pinned": (i32, [vp]),
         "b200v_memcpy_h2d": (i32, [i32, vp, vp, sz]),
         "b200v_memcpy_d2h": (i32, [i32, vp, vp, sz]),
     }
@@ -125,8 +127,8 @@ EXPORTED_SYMBOLS = [
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
     "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_shard_range", "b200v_sharded_create",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
-    "b200v_sharded_last_error", "b200v_device_alloc", "b200v_device_free",
-    "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
+    "b200v_sharded_last_error", "b200v_bind_host_to_device", "b200v_device_alloc", "b200v_device_free",
+    "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_host_is_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
 ]
 
 

@@ -44,6 +44,8 @@ const kvref_vtable* kvref_at(int i);
  * Set before create; applies to wy_* decoders created afterwards (process-global, test use only).
  * kind: 0 = defaults from main.cpp (soft8 for u8, soft16 for u16), 1 = hard8 (u8 only). */
 void kvref_wy_set_config_kind(int kind);
+/* williamyang instances only: the sum of decoder_t::update<uint64_t>()'s return values since the last init. */
+uint64_t kvref_wy_error_sum(void* h);
 
 #ifdef __cplusplus
 }

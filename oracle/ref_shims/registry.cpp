@@ -15,7 +15,6 @@ static const kvref_vtable* const g_all[] = {
     DECL(spiral27) DECL(spiral29) DECL(spiral47) DECL(spiral49) DECL(spiral615)
     WY4(k7r2) WY4(k7r3) WY4(k7r4) WY4(k9r2) WY4(k9r4) WY4(k15r6) WY4(k24r2)
     DECL(wy_sse_u16_k5r2)
-DECL(wy_sse_u16_k5r2)
 };
 extern "C" int kvref_count(void) { return (int)(sizeof(g_all) / sizeof(g_all[0])); }
 extern "C" const kvref_vtable* kvref_at(int i) { return (i >= 0 && i < kvref_count()) ? g_all[i] : 0; }

@@ -46,8 +46,13 @@ static WyCfg<int16_t, uint16_t> make_cfg_u16(size_t R) {
     return { hi, lo, c };
 }
 
+/* sum of update<>()'s return values since the last init: the renormalisation minima the reference's callers add to
+ * get_error() (run_snr_ber.cpp:369-371, run_simple.cpp:78-79) */
+struct WyBase { uint64_t err_sum = 0; };
+extern "C" uint64_t kvref_wy_error_sum(void* h) { return ((WyBase*)h)->err_sum; }
+
 template <size_t K, size_t R, typename soft_t, typename error_t, class decoder_t>
-struct WyInst {
+struct WyInst : WyBase {
     using Core = ViterbiDecoder_Core<K, R, error_t, soft_t>;
     using Table = ViterbiBranchTable<K, R, soft_t>;
     std::unique_ptr<Table> table;
@@ -63,10 +68,10 @@ struct WyInst {
         p->core->set_traceback_length(size_t(len) - (K - 1));
         return p;
     }
-    static int init(void* h, int s) { ((WyInst*)h)->core->reset(size_t(s)); return 0; }
+    static int init(void* h, int s) { ((WyInst*)h)->core->reset(size_t(s)); ((WyInst*)h)->err_sum = 0; return 0; }
     static void update(void* h, const void* syms, int nsteps) {
         auto* p = (WyInst*)h;
-        decoder_t::template update<uint64_t>(*p->core, (const soft_t*)syms, size_t(nsteps) * R);
+        p->err_sum += decoder_t::template update<uint64_t>(*p->core, (const soft_t*)syms, size_t(nsteps) * R);
     }
     static int chainback(void* h, uint8_t* data, unsigned nbits, unsigned endstate) {
         ((WyInst*)h)->core->chainback(data, nbits, endstate);

@@ -60,6 +60,8 @@ static const int POLY_K9R2[] = { 0x1af, 0x11d };
 static const int POLY_K9R4[] = { 501, 441, 331, 315 };
 static const int POLY_K15R6[] = { 042631, 047245, 056507, 073363, 077267, 064537 };
 static const int POLY_K24R2[] = { 062650457, 062650455 };
+static const int POLY_K3R2[] = { 7, 5 };                         /* helpers/common_codes.h:21 (Basic K=3) */
+static const int POLY_K5R2[] = { 23, 25 };                       /* helpers/common_codes.h:22 (Basic K=5) */
 
 static const int* std_poly(int K, int R) {
     if (K == 7 && R == 2) return POLY_K7R2;
@@ -69,6 +71,8 @@ static const int* std_poly(int K, int R) {
     if (K == 9 && R == 4) return POLY_K9R4;
     if (K == 15 && R == 6) return POLY_K15R6;
     if (K == 24 && R == 2) return POLY_K24R2;
+    if (K == 3 && R == 2) return POLY_K3R2;
+    if (K == 5 && R == 2) return POLY_K5R2;
     return NULL;
 }
 
@@ -121,6 +125,7 @@ struct kvo_decoder {
     int32_t* old_m;        /* [S] */
     int32_t* new_m;        /* [S] */
     uint8_t* dec;          /* [len][S/8] canonical decision vectors */
+    uint64_t renorm_sum;   /* sum of the minima subtracted by renormalisations since init (wy: update()'s return value) */
 };
 
 kvo_decoder* kvo_create(const kvo_codec* c, int len) {
@@ -163,6 +168,7 @@ int kvo_init(kvo_decoder* d, int starting_state) {
     for (int i = 0; i < d->S; i++) d->old_m[i] = d->c.init_other;
     d->old_m[starting_state & (d->S - 1)] = d->c.init_start;
     d->cursor = 0;
+    d->renorm_sum = 0;
     return 0;
 }
 
@@ -225,63 +231,93 @@ static int32_t branch_metric(const kvo_decoder* d, const int32_t* sym, unsigned 
 
 /* One trellis step: old_m -> new_m, decision row `row`. Butterfly j (SURVEY 8 notation):
  *   lo = old[j], hi = old[j+S/2]; new[2j] = sel(lo+BM, hi+(C-BM)); new[2j+1] = sel(lo+(C-BM), hi+BM) */
+static inline __attribute__((always_inline)) unsigned butterfly(const kvo_codec* c, const int32_t* restrict bmtab,
+                                                                const uint8_t* restrict cwp, const int32_t* restrict old_m,
+                                                                int32_t* restrict new_m, int H, int j, const int policy) {
+    const int32_t bm = bmtab[cwp[j]];
+    const int32_t lo = old_m[j], hi = old_m[j + H];
+    int32_t m0, m1, m2, m3, s0, s1;
+    int d0, d1;
+    switch (policy) {
+    case KVO_KA9Q_U8_MOD: {
+        /* viterbi27_sse2.cpp:148-158: wrapping u8 adds, decision = (int8)(a-b) > 0, tie -> 0 */
+        const int32_t cm = 15 - bm;
+        m0 = (lo + bm) & 255; m1 = (hi + cm) & 255; m2 = (lo + cm) & 255; m3 = (hi + bm) & 255;
+        d0 = (int8_t)(uint8_t)(m0 - m1) > 0;
+        d1 = (int8_t)(uint8_t)(m2 - m3) > 0;
+        s0 = d0 ? m1 : m0; s1 = d1 ? m3 : m2;
+        break;
+    }
+    case KVO_KA9Q_S16_615: {
+        /* viterbi615_sse2.cpp:136-148: adds_epi16, min_epi16, decision = (min == hi-path), tie -> 1 */
+        const int32_t cm = (int16_t)(c->max_error - bm);
+        m0 = sat_s16(lo + bm); m1 = sat_s16(hi + cm); m2 = sat_s16(lo + cm); m3 = sat_s16(hi + bm);
+        s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
+        d0 = s0 == m1; d1 = s1 == m3;
+        break;
+    }
+    case KVO_KA9Q_S16_224: {
+        /* viterbi224_sse2.cpp:160-194: decision = lo-path > hi-path (cmpgt_epi16), tie -> 0 */
+        const int32_t cm = (int16_t)(c->max_error - bm);
+        m0 = sat_s16(lo + bm); m1 = sat_s16(hi + cm); m2 = sat_s16(lo + cm); m3 = sat_s16(hi + bm);
+        d0 = m0 > m1; d1 = m2 > m3;
+        s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
+        break;
+    }
+    case KVO_SPIRAL_R2: case KVO_SPIRAL_R4: case KVO_SPIRAL_615: case KVO_WY_U8: {
+        /* spiral27.cpp:171-181 ; spiral615.cpp:240-250 ; sse_u8.h:105-114:
+         * subs_epu8(C,BM), adds_epu8, min_epu8, decision = (min == hi-path), tie -> 1 */
+        const int32_t cm = sat_u8(c->max_error - bm);
+        m0 = sat_u8(lo + bm); m1 = sat_u8(hi + cm); m2 = sat_u8(lo + cm); m3 = sat_u8(hi + bm);
+        s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
+        d0 = s0 == m1; d1 = s1 == m3;
+        break;
+    }
+    default: { /* KVO_WY_U16: sse_u16.h:105-115 */
+        const int32_t cm = sat_u16(c->max_error - bm);
+        m0 = sat_u16(lo + bm); m1 = sat_u16(hi + cm); m2 = sat_u16(lo + cm); m3 = sat_u16(hi + bm);
+        s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
+        d0 = s0 == m1; d1 = s1 == m3;
+        break;
+    }
+    }
+    new_m[2 * j] = s0; new_m[2 * j + 1] = s1;
+    return (unsigned)d0 | ((unsigned)d1 << 1);
+}
+
+/* the butterflies of one step; `policy` is a compile-time constant at every call site (see step()), so the switch
+ * folds away and the loop is specialised per policy; a decision byte (four butterflies) is assembled in a register */
+static inline __attribute__((always_inline)) void butterflies(kvo_decoder* d, const int32_t* bmtab, uint8_t* restrict row,
+                                                              const int policy) {
+    const kvo_codec* c = &d->c;
+    const int H = d->S / 2;
+    const uint8_t* restrict cwp = d->cw;
+    const int32_t* restrict old_m = d->old_m;
+    int32_t* restrict new_m = d->new_m;
+    int j = 0;
+    for (; j + 4 <= H; j += 4) {
+        unsigned b = butterfly(c, bmtab, cwp, old_m, new_m, H, j, policy);
+        b |= butterfly(c, bmtab, cwp, old_m, new_m, H, j + 1, policy) << 2;
+        b |= butterfly(c, bmtab, cwp, old_m, new_m, H, j + 2, policy) << 4;
+        b |= butterfly(c, bmtab, cwp, old_m, new_m, H, j + 3, policy) << 6;
+        row[j >> 2] = (uint8_t)b;
+    }
+    for (; j < H; j++)      /* K = 3: two butterflies */
+        row[(2 * j) >> 3] |= (uint8_t)(butterfly(c, bmtab, cwp, old_m, new_m, H, j, policy) << ((2 * j) & 7));
+}
+
 static void step(kvo_decoder* d, const int32_t* sym, uint8_t* row) {
     const kvo_codec* c = &d->c;
-    const int S = d->S, H = S / 2;
+    const int S = d->S;
     memset(row, 0, row_bytes(S));
     int32_t bmtab[1 << KVO_MAX_R];   /* the branch metric depends on j only through its code word */
     for (unsigned w = 0; w < (1u << c->R); w++) bmtab[w] = branch_metric(d, sym, w);
-    for (int j = 0; j < H; j++) {
-        const int32_t bm = bmtab[d->cw[j]];
-        const int32_t lo = d->old_m[j], hi = d->old_m[j + H];
-        int32_t m0, m1, m2, m3, s0, s1;
-        int d0, d1;
-        switch (c->policy) {
-        case KVO_KA9Q_U8_MOD: {
-            /* viterbi27_sse2.cpp:148-158: wrapping u8 adds, decision = (int8)(a-b) > 0, tie -> 0 */
-            const int32_t cm = 15 - bm;
-            m0 = (lo + bm) & 255; m1 = (hi + cm) & 255; m2 = (lo + cm) & 255; m3 = (hi + bm) & 255;
-            d0 = (int8_t)(uint8_t)(m0 - m1) > 0;
-            d1 = (int8_t)(uint8_t)(m2 - m3) > 0;
-            s0 = d0 ? m1 : m0; s1 = d1 ? m3 : m2;
-            break;
-        }
-        case KVO_KA9Q_S16_615: {
-            /* viterbi615_sse2.cpp:136-148: adds_epi16, min_epi16, decision = (min == hi-path), tie -> 1 */
-            const int32_t cm = (int16_t)(c->max_error - bm);
-            m0 = sat_s16(lo + bm); m1 = sat_s16(hi + cm); m2 = sat_s16(lo + cm); m3 = sat_s16(hi + bm);
-            s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
-            d0 = s0 == m1; d1 = s1 == m3;
-            break;
-        }
-        case KVO_KA9Q_S16_224: {
-            /* viterbi224_sse2.cpp:160-194: decision = lo-path > hi-path (cmpgt_epi16), tie -> 0 */
-            const int32_t cm = (int16_t)(c->max_error - bm);
-            m0 = sat_s16(lo + bm); m1 = sat_s16(hi + cm); m2 = sat_s16(lo + cm); m3 = sat_s16(hi + bm);
-            d0 = m0 > m1; d1 = m2 > m3;
-            s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
-            break;
-        }
-        case KVO_SPIRAL_R2: case KVO_SPIRAL_R4: case KVO_SPIRAL_615: case KVO_WY_U8: {
-            /* spiral27.cpp:171-181 ; spiral615.cpp:240-250 ; sse_u8.h:105-114:
-             * subs_epu8(C,BM), adds_epu8, min_epu8, decision = (min == hi-path), tie -> 1 */
-            const int32_t cm = sat_u8(c->max_error - bm);
-            m0 = sat_u8(lo + bm); m1 = sat_u8(hi + cm); m2 = sat_u8(lo + cm); m3 = sat_u8(hi + bm);
-            s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
-            d0 = s0 == m1; d1 = s1 == m3;
-            break;
-        }
-        default: { /* KVO_WY_U16: sse_u16.h:105-115 */
-            const int32_t cm = sat_u16(c->max_error - bm);
-            m0 = sat_u16(lo + bm); m1 = sat_u16(hi + cm); m2 = sat_u16(lo + cm); m3 = sat_u16(hi + bm);
-            s0 = m0 < m1 ? m0 : m1; s1 = m2 < m3 ? m2 : m3;
-            d0 = s0 == m1; d1 = s1 == m3;
-            break;
-        }
-        }
-        d->new_m[2 * j] = s0; d->new_m[2 * j + 1] = s1;
-        row[(2 * j) >> 3] |= (uint8_t)(d0 << ((2 * j) & 7));
-        row[(2 * j + 1) >> 3] |= (uint8_t)(d1 << ((2 * j + 1) & 7));
+    switch (c->policy) {
+    case KVO_KA9Q_U8_MOD: butterflies(d, bmtab, row, KVO_KA9Q_U8_MOD); break;
+    case KVO_KA9Q_S16_615: butterflies(d, bmtab, row, KVO_KA9Q_S16_615); break;
+    case KVO_KA9Q_S16_224: butterflies(d, bmtab, row, KVO_KA9Q_S16_224); break;
+    case KVO_WY_U16: butterflies(d, bmtab, row, KVO_WY_U16); break;
+    default: butterflies(d, bmtab, row, KVO_WY_U8); break;      /* the four u8-saturating policies share one body */
     }
 
     /* renormalisation: checked after every step on new[0] only */
@@ -296,6 +332,7 @@ static void step(kvo_decoder* d, const int32_t* sym, uint8_t* row) {
             for (int i = 1; i < S; i++) if (m[i] < mn) mn = m[i];
             const int32_t adj = mn + 32768;                       /* bring the minimum down to SHRT_MIN */
             for (int i = 0; i < S; i++) m[i] = (int16_t)(uint16_t)(m[i] - adj);  /* sub_epi16, wrapping */
+            d->renorm_sum += (uint64_t)adj;
         }
         break;
     case KVO_SPIRAL_R2: case KVO_SPIRAL_R4: case KVO_SPIRAL_615:   /* spiral27.cpp:236-254, spiral615.cpp:31-40 */
@@ -303,6 +340,7 @@ static void step(kvo_decoder* d, const int32_t* sym, uint8_t* row) {
             mn = m[0];
             for (int i = 1; i < S; i++) if (m[i] < mn) mn = m[i];
             for (int i = 0; i < S; i++) m[i] -= mn;
+            d->renorm_sum += (uint64_t)mn;
         }
         break;
     case KVO_WY_U8: case KVO_WY_U16:                               /* sse_u8.h:63-65,127-154 */
@@ -310,6 +348,7 @@ static void step(kvo_decoder* d, const int32_t* sym, uint8_t* row) {
             mn = m[0];
             for (int i = 1; i < S; i++) if (m[i] < mn) mn = m[i];
             for (int i = 0; i < S; i++) m[i] -= mn;
+            d->renorm_sum += (uint64_t)mn;        /* sse_u8.h:63-65: update() returns the sum of these minima */
         }
         break;
     }
@@ -337,6 +376,8 @@ void kvo_update(kvo_decoder* d, const void* syms, int nsteps) {
         d->cursor++;
     }
 }
+
+uint64_t kvo_renorm_sum(const kvo_decoder* d) { return d->renorm_sum; }
 
 void kvo_get_decisions(kvo_decoder* d, int step0, int nsteps, uint8_t* out) {
     memcpy(out, d->dec + (size_t)step0 * row_bytes(d->S), (size_t)nsteps * row_bytes(d->S));

@@ -65,6 +65,10 @@ void kvo_get_decisions(kvo_decoder* d, int step0, int nsteps, uint8_t* out);
 /* current path metrics as S elements of kvo_metric_bytes() each (u8 / i16 / u16 raw bits) */
 void kvo_get_metrics(kvo_decoder* d, void* out);
 int  kvo_steps_done(const kvo_decoder* d);
+/* Sum of the minima subtracted by the renormalisations since kvo_init: what the williamyang decoders' update<>()
+ * returns, summed over the calls (viterbi_decoder_sse_u8.h:57-69; consumed as accumulated_error + get_error() by
+ * run_snr_ber.cpp:369-371). Tracked for every renormalising policy. */
+uint64_t kvo_renorm_sum(const kvo_decoder* d);
 
 /* ---- test-input generation (restates src/util.h:15-62 + convolutional_encoder_shift_register.h:42-62) ---- */
 

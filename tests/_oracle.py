@@ -17,6 +17,34 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_SO = os.path.join(ORACLE_DIR, "liboracle.so")
 REF_SO = os.path.join(ORACLE_DIR, "_ref", "libkvref.so")
+REF_NATIVE_SO = os.path.join(ORACLE_DIR, "_ref", "libkvref_native.so")          # the reference preset's -march=native build
+REF_NATIVE_FLAGS = os.path.join(ORACLE_DIR, "_ref", "native_cpu_flags.txt")     # ISA flags of the host that built it
+
+
+def native_ref_usable():
+    """libkvref_native.so may run here iff this host has every CPU flag of the host that compiled it."""
+    import re
+    isa = re.compile(r"^(sse|ssse|avx|amx|bmi|fma|f16c|adx|aes|vaes|sha|gfni|movbe|movdir|popcnt|abm|pclmul|vpclmul|rdrand|rdseed|"
+                     r"clflushopt|clwb|cldemote|xsave|fsgsbase|rdpid|pku|ospke|waitpkg|serialize|lahf|cx16|erms|fsrm|invpcid|rtm|hle)")
+    try:
+        need = set(f for f in open(REF_NATIVE_FLAGS).read().split() if isa.match(f))
+        have = set()
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("flags"):
+                have = set(line.split(":", 1)[1].split())
+                break
+        return os.path.exists(REF_NATIVE_SO) and bool(need) and need <= have
+    except OSError:
+        return False
+
+
+def use_native_ref():
+    """Point Ref at the -march=native build (bench.py's CPU arm; call before the first ref_lib()). Returns True if done."""
+    global REF_SO
+    if _ref is None and native_ref_usable():
+        REF_SO = REF_NATIVE_SO
+        return True
+    return False
 
 MAX_R = 8
 
@@ -56,6 +84,8 @@ def oracle_lib():
         lib.kvo_get_decisions.restype = None
         lib.kvo_get_metrics.argtypes = [C.c_void_p, C.c_void_p]
         lib.kvo_get_metrics.restype = None
+        lib.kvo_renorm_sum.argtypes = [C.c_void_p]
+        lib.kvo_renorm_sum.restype = C.c_uint64
         lib.kvo_encode_bits.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p, C.c_size_t, C.c_void_p]
         lib.kvo_encode_bits.restype = None
         lib.kvo_random_bytes.argtypes = [C.c_uint64, C.c_uint64, C.c_void_p, C.c_size_t]
@@ -155,6 +185,10 @@ class Oracle(_Decoder):
         self.lib.kvo_get_metrics(self.h, out.ctypes.data)
         return out
 
+    def renorm_sum(self):
+        """sum of the renormalisation minima since init (the williamyang update()'s return value, accumulated)"""
+        return int(self.lib.kvo_renorm_sum(self.h))
+
     def close(self):
         if self.h:
             self.lib.kvo_destroy(self.h)
@@ -191,6 +225,9 @@ def ref_lib():
         lib.kvref_count.restype = C.c_int
         lib.kvref_at.restype = C.POINTER(_KvrefVtable)
         lib.kvref_at.argtypes = [C.c_int]
+        if hasattr(lib, "kvref_wy_error_sum"):
+            lib.kvref_wy_error_sum.restype = C.c_uint64
+            lib.kvref_wy_error_sum.argtypes = [C.c_void_p]
         if hasattr(lib, "kvref_time_decode"):
             lib.kvref_time_decode.restype = C.c_double
             lib.kvref_time_decode.argtypes = [C.POINTER(_KvrefVtable), C.c_void_p, C.c_void_p, C.c_int, C.c_size_t,
@@ -242,6 +279,11 @@ class Ref(_Decoder):
         out = np.zeros(self.S, dtype=metric_dtype(self.codec))
         self.vt.get_metrics(self.h, out.ctypes.data)
         return out
+
+    def renorm_sum(self):
+        """williamyang decoders: sum of update<uint64_t>()'s return values since init"""
+        assert self.vt.name.decode().startswith("wy_")
+        return int(ref_lib().kvref_wy_error_sum(self.h))
 
     def time_decode(self, pool, T, nbits, seconds):
         """Decode the frames of `pool` ([n][T*R] symbols) in a C loop for ~`seconds` (GIL released).

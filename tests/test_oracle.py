@@ -12,12 +12,25 @@ GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.np
 ALL_NAMES = [
     "ka9q27", "ka9q29", "ka9q615", "ka9q224", "spiral27", "spiral29", "spiral47", "spiral49", "spiral615",
 ] + [f"wy_{simd}_{w}_{kr}" for kr in ("k7r2", "k7r3", "k7r4", "k9r2", "k9r4", "k15r6", "k24r2")
-     for simd in ("sse", "avx") for w in ("u8", "u16")]
+     for simd in ("sse", "avx") for w in ("u8", "u16")] + ["wy_sse_u16_k5r2"]
 
 
 @pytest.fixture(scope="module")
 def golden():
     return np.load(GOLDEN)
+
+
+def extreme_patterns(c, T):
+    """Symbol sequences that saturate, tie on every butterfly and renormalise often, plus hard-decision adversarial ones
+    (runs and alternations of the two extreme values at several periods)."""
+    lo, hi = o.soft_range(c)
+    n = T * c.R
+    k = np.arange(n)
+    pats = [np.full(n, lo), np.full(n, hi), np.where(k % 2, lo, hi), np.full(n, (lo + hi) // 2),
+            np.where((k // c.R) % 3 == 0, hi, lo),
+            np.where((k // c.R) % 2, hi, lo), np.where((k // (c.R * (c.K - 1))) % 2, hi, lo),
+            np.where((k * 7 // 5) % 3 == 1, hi, lo), np.where((k // c.R) % (c.K + 1) < 2, lo, (lo + hi + 1) // 2)]
+    return [p.astype(o.sym_dtype(c)) for p in pats]
 
 
 def sha(a):
@@ -28,8 +41,11 @@ def sha(a):
 def test_oracle_matches_golden(golden, name):
     """Known-answer test: decisions, metrics, decoded bytes and return code of the reference."""
     c = o.codec_by_name(name)
-    for ci in range(3):
+    for ci in range(4):
         key = f"{name}/{ci}"
+        if key + "/syms" not in golden:
+            assert ci == 3 and c.K != 24      # the renormalising fourth case exists for K=24 only
+            continue
         syms = golden[key + "/syms"]
         T = syms.size // c.R
         nbits = T - (c.K - 1)
@@ -45,7 +61,59 @@ def test_oracle_matches_golden(golden, name):
         if key + "/dec_head" in golden:
             assert np.array_equal(dec[:4], golden[key + "/dec_head"])
             assert np.array_equal(dec[-4:], golden[key + "/dec_tail"])
+        if key + "/error_sum" in golden:      # decoder_t::update<uint64_t>()'s return value
+            assert q.renorm_sum() == int(golden[key + "/error_sum"]), f"{key}: sum of renormalisation minima differs"
+            if ci == 3:
+                assert q.renorm_sum() > 0, f"{key}: the K=24 renormalisation case did not renormalise"
         q.close()
+
+
+@pytest.mark.skipif(not o.ref_available(), reason="oracle/_ref/libkvref.so not built (needs /root/reference)")
+def test_golden_recipe_reproduces_the_committed_fixtures(golden):
+    """tests/golden/make_golden.py must run at HEAD and give exactly the committed .npz (every array)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(os.path.dirname(GOLDEN), "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    store = mg.generate()
+    assert sorted(store) == sorted(golden.files)
+    assert sorted(store["names"].tolist()) == sorted(ALL_NAMES)
+    for k in golden.files:
+        assert np.array_equal(np.asarray(store[k]), golden[k]), k
+
+
+K24_PIN = [("ka9q224", "erased"), ("ka9q224", "random"), ("wy_sse_u8_k24r2", "random"), ("wy_avx_u8_k24r2", "erased"),
+           ("wy_sse_u16_k24r2", "erased"), ("wy_avx_u16_k24r2", "random")]
+
+
+@pytest.mark.skipif(not o.ref_available(), reason="oracle/_ref/libkvref.so not built (needs /root/reference)")
+@pytest.mark.parametrize("name,kind", K24_PIN)
+def test_oracle_k24_renormalisation_matches_compiled_reference(name, kind):
+    """viterbi224_sse2.cpp:226-246 and the williamyang renormalise (sse_u8.h:127-154, sse_u16.h:152-177) at K=24 need
+    hundreds of steps before new[0] reaches the threshold: 263-step frames of erased symbols (every path costs the
+    same) and of uniformly random symbols, split over two update calls, against the compiled reference -- decision
+    vectors of every step, final metrics, decoded bytes and (williamyang) the sum of the subtracted minima."""
+    c = o.codec_by_name(name)
+    lo, hi = o.soft_range(c)
+    T = 263
+    rng = np.random.default_rng(224)
+    syms = (np.full(T * c.R, (lo + hi + 1) // 2) if kind == "erased" else rng.integers(lo, hi + 1, T * c.R)).astype(o.sym_dtype(c))
+    r, q = o.Ref(name, T), o.Oracle(c, T)
+    for d in (r, q):
+        d.init(0)
+        d.update(syms[:211 * c.R], 211)
+        d.update(syms[211 * c.R:], T - 211)
+    assert np.array_equal(r.decisions(0, T), q.decisions(0, T)), "decision vectors differ"
+    assert np.array_equal(r.metrics(), q.metrics()), "metrics differ"
+    nbits = T - (c.K - 1)
+    assert np.array_equal(r.chainback(nbits), q.chainback(nbits))
+    if name.startswith("wy_"):
+        assert r.renorm_sum() == q.renorm_sum()
+    if kind == "erased":        # must have renormalised: otherwise new[0] would have passed the threshold long ago
+        assert q.renorm_sum() > 0
+        thr = c.renorm_threshold
+        assert int(q.metrics().astype(np.int16 if c.policy == 2 else np.int64)[0]) < thr
+    r.close(); q.close()
 
 
 def test_golden_noiseless_round_trip(golden):
@@ -73,6 +141,8 @@ def test_oracle_matches_compiled_reference(name, sigma):
         assert np.array_equal(rd, qd), "decision vectors differ"
         assert np.array_equal(r.metrics(), q.metrics()), "metrics differ"
         assert np.array_equal(ro, qo), "decoded bytes differ"
+        if name.startswith("wy_"):
+            assert r.renorm_sum() == q.renorm_sum(), "sum of renormalisation minima (update()'s return value) differs"
         r.close(); q.close()
 
 
@@ -101,15 +171,11 @@ def test_oracle_streaming_updates_match_reference(name):
 @pytest.mark.skipif(not o.ref_available(), reason="oracle/_ref/libkvref.so not built")
 def test_oracle_extreme_inputs_match_reference():
     """All-zero / all-max / alternating symbols: saturation, ties on every butterfly, renormalisation."""
-    for name in ["ka9q27", "spiral27", "spiral47", "spiral29", "wy_sse_u8_k7r2", "wy_sse_u16_k7r4",
-                 "spiral615", "ka9q615", "wy_avx_u8_k15r6"]:
+    for name in ["ka9q27", "ka9q29", "spiral27", "spiral47", "spiral29", "spiral49", "wy_sse_u8_k7r2", "wy_sse_u8_k9r2",
+                 "wy_sse_u16_k7r4", "spiral615", "ka9q615", "wy_avx_u8_k15r6"]:
         c = o.codec_by_name(name)
-        lo, hi = o.soft_range(c)
         T = 200 if c.K == 15 else 600
-        n = T * c.R
-        pats = [np.full(n, lo), np.full(n, hi), np.where(np.arange(n) % 2, lo, hi),
-                np.full(n, (lo + hi) // 2), np.where((np.arange(n) // c.R) % 3 == 0, hi, lo)]
-        for p in pats:
+        for p in extreme_patterns(c, T):
             syms = p.astype(o.sym_dtype(c))
             r, q = o.Ref(name, T), o.Oracle(c, T)
             nbits = T - (c.K - 1)
@@ -119,6 +185,54 @@ def test_oracle_extreme_inputs_match_reference():
             assert np.array_equal(r.metrics(), q.metrics()), name
             assert np.array_equal(ro, qo), name
             r.close(); q.close()
+
+
+def test_modular_compare_bound_k7_k9():
+    """ka9q27 / ka9q29 decide with (int8)(m0 - m1) > 0 on wrapping u8 metrics (viterbi27_sse2.cpp:155-156). The CUDA
+    kernels keep unwrapped metrics and compare plainly: the same decision iff |m0 - m1| <= 127 at every butterfly.
+    Proof (csrc/acs_k7.cu, csrc/acs_grp.cu headers): the two candidates of a butterfly are the best paths into the new
+    state through old states j and j + S/2; from a common state K-1 steps back those paths take the same inputs but
+    the first, so their codewords differ at step m exactly by the taps of register position m-1: both taps -> the
+    branch metrics differ by <= 15, one tap -> <= 8, none -> 0. Summed over the K positions of main.cpp's polynomials:
+    76 (K=7), 92 (K=9) once K-1 steps have run; before that every metric lies in [0, 63 + 7t], so the difference is at
+    most 78 + 7t <= 113 (K=7), 127 (K=9). This test tracks the unwrapped recurrence on random, hard-decision,
+    erasure-mixed and the extreme patterns and checks both bounds."""
+    for name, steady, transient in (("ka9q27", 76, 113), ("ka9q29", 92, 127)):
+        c = o.codec_by_name(name)
+        S, H = 1 << (c.K - 1), 1 << (c.K - 2)
+        # the analytic steady-state bound from the tap patterns of the two polynomials
+        taps = [((c.poly[0] >> p) & 1) + ((c.poly[1] >> p) & 1) for p in range(c.K)]
+        assert sum({2: 15, 1: 8, 0: 0}[x] for x in taps) == steady
+        cw = np.array([sum((bin((2 * j) & c.poly[i]).count("1") & 1) << i for i in range(2)) for j in range(H)])
+        T = 400
+        rng = np.random.default_rng(29)
+        seqs = list(extreme_patterns(c, T)) + [rng.integers(0, 256, T * 2), rng.choice([0, 255], T * 2),
+                                              rng.choice([0, 128, 255], T * 2), rng.choice([0, 15, 240, 255], T * 2)]
+        worst_t, worst_s = 0, 0
+        for syms in seqs:
+            syms = np.asarray(syms, dtype=np.int64)
+            for start in (0, 5):
+                m = np.full(S, 63, dtype=np.int64)
+                m[start] = 0
+                for t in range(T):
+                    s0, s1 = syms[2 * t], syms[2 * t + 1]
+                    x0 = np.where(cw & 1, s0 ^ 255, s0)
+                    x1 = np.where(cw & 2, s1 ^ 255, s1)
+                    bm = ((x0 + x1 + 1) >> 1) >> 4
+                    lo_, hi_ = m[:H], m[H:]
+                    a0, a1, b0, b1 = lo_ + bm, hi_ + 15 - bm, lo_ + 15 - bm, hi_ + bm
+                    d = max(int(np.abs(a0 - a1).max()), int(np.abs(b0 - b1).max()))
+                    if t < c.K - 1:
+                        worst_t = max(worst_t, d)
+                        assert d <= 78 + 7 * t
+                    else:
+                        worst_s = max(worst_s, d)
+                    n = np.empty(S, dtype=np.int64)
+                    n[0::2] = np.minimum(a0, a1)
+                    n[1::2] = np.minimum(b0, b1)
+                    m = n
+                    assert int(m.max() - m.min()) < 128        # what the kernels' unwrap around state 0 needs
+        assert worst_t <= transient and worst_s <= steady, (name, worst_t, worst_s)
 
 
 def test_encoder_matches_definition():

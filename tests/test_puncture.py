@@ -113,3 +113,25 @@ def test_gpu_depuncture_and_dab_fic_round_trip(name):
         assert np.array_equal(out[f], qo), f
         q.close()
     assert np.array_equal(out[0], datas[0])                    # the noiseless frame decodes to the data
+
+
+@pytest.mark.gpu
+def test_gpu_depuncture_more_than_65535_frames():
+    """The headline batch has 1 Mi frames: the frame index must not live on a 65535-capped grid dimension."""
+    import torch
+    import ka9q_viterbi_comparison_b200 as kv
+    n_frames, n_out, R = 70001, 96, 4
+    code = po.PI_15
+    kept = int(sum(code[k % len(code)] for k in range(n_out)))
+    rng = np.random.default_rng(5)
+    tx = rng.integers(-3, 4, (n_frames, kept)).astype(np.int8)
+    d_tx = torch.from_numpy(tx.view(np.uint8).copy()).cuda()
+    d_syms = torch.zeros(n_frames * n_out, dtype=torch.uint8, device="cuda")
+    with kv.BatchDecoder(kv.WY_U8, n_out // R, n_frames, K=7, R=R, poly=[109, 79, 83, 109]) as dec:
+        used = dec.depuncture_dev(d_tx, kept, 0, code, d_syms, n_out, 0, n_out, 0)
+        dec.sync()
+    assert used == kept
+    got = d_syms.cpu().numpy().view(np.int8).reshape(n_frames, n_out)
+    for f in (0, 65535, 65536, n_frames - 1):
+        want, _ = po.depuncture(tx[f], code, n_out, 0, R)
+        assert np.array_equal(got[f], want), f

@@ -19,6 +19,7 @@ constexpr int ITERS = 4096;
         }                                                                             \
         unsigned r = 0;                                                               \
         for (int i = 0; i < ILP; i++) r ^= a[i];                                      \
+        r ^= b;                                                                       \
         if (r == 0x12345678u) out[0] = r;                                             \
     }
 
@@ -45,6 +46,30 @@ DEFINE_KERNEL(k_mix_imad_lop3, { if (i & 1) a[i] = a[i] * b + Y; else a[i] = (a[
 DEFINE_KERNEL(k_mix_imad_viaddmin, { if (i & 1) a[i] = a[i] * b + Y; else a[i] = __viaddmin_u16x2(a[i], Y, c); })
 DEFINE_KERNEL(k_mix_hadd2_viaddmin, { if (i & 1) { __half2 h = __hadd2(H2(a[i]), H2(Y)); a[i] = *reinterpret_cast<unsigned*>(&h); } else a[i] = __viaddmin_u16x2(a[i], Y, c); })
 DEFINE_KERNEL(k_mix_lop3_viaddmin, { if (i & 1) a[i] = (a[i] & Y) ^ c; else a[i] = __viaddmin_u16x2(a[i], Y, c); })
+
+// ---- round 2: candidates for taking the decision collection off the issue budget -----------------------------------
+// HSET2 with a mask result (0xffff / 0 per half): which pipe, and does it issue beside the DPX ops and IMAD?
+__device__ __forceinline__ unsigned hne2m(unsigned a, unsigned b) { unsigned d; asm("set.ne.u32.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ unsigned imad(unsigned a, unsigned b, unsigned c) { unsigned d; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+__device__ __forceinline__ unsigned iadd3(unsigned a, unsigned b, unsigned z) { unsigned d; asm("{\n\t.reg .u32 t;\n\tadd.u32 t, %1, %2;\n\tadd.u32 %0, t, %3;\n\t}" : "=r"(d) : "r"(a), "r"(b), "r"(z)); return d; }
+DEFINE_KERNEL(k_hset2, a[i] = hne2m(a[i], Y) ^ 0u)
+DEFINE_KERNEL(k_mix_hset2_viaddmin, { if (i & 1) a[i] = hne2m(a[i], Y); else a[i] = __viaddmin_u16x2(a[i], Y, c); })
+DEFINE_KERNEL(k_mix_hset2_imad, { if (i & 1) a[i] = hne2m(a[i], Y); else a[i] = imad(a[i], b, Y); })
+DEFINE_KERNEL(k_mix_hset2_hadd2, { if (i & 1) a[i] = hne2m(a[i], Y); else { __half2 h = __hadd2(H2(a[i]), H2(Y)); a[i] = *reinterpret_cast<unsigned*>(&h); } })
+// three pipes at once: DPX (ALU) + IMAD (FMA heavy) + HSET2
+DEFINE_KERNEL(k_mix3_viaddmin_imad_hset2, { if ((i & 3) == 0) a[i] = imad(a[i], b, Y); else if ((i & 3) == 2) a[i] = hne2m(a[i], Y); else a[i] = __viaddmin_u16x2(a[i], Y, c); })
+// the fused ACS body for one packed pair of new states: t = lo path (add), n = min(hi + Wc, t) (VIADDMNMX), mask = (n != t)
+// (HSET2), S = 2 S + mask (Horner on IMAD or IADD3): 4 instructions per 2 new states and 2 decisions
+#define ACS_FUSED(ADD_T, HORNER)                                                                  \
+    { const unsigned t = ADD_T; const unsigned n = __viaddmin_u16x2(Y, c, t); const unsigned m = hne2m(n, t); \
+      b = HORNER; a[i] = n; }
+DEFINE_KERNEL(k_acs_fused_fma_t_alu_h, ACS_FUSED(imad(a[i], seed | 1u, c), iadd3(b, b, m)))
+DEFINE_KERNEL(k_acs_fused_alu_t_fma_h, ACS_FUSED(iadd3(a[i], c, seed & 0u), imad(b, 2u + (seed & 0u), m)))
+DEFINE_KERNEL(k_acs_fused_alu_t_alu_h, ACS_FUSED(iadd3(a[i], c, seed & 0u), iadd3(b, b, m)))
+DEFINE_KERNEL(k_acs_fused_fma_t_fma_h, ACS_FUSED(imad(a[i], seed | 1u, c), imad(b, 2u + (seed & 0u), m)))
+// today's body: two adds, VIMNMX with predicate outputs, two predicated adds: 5 instructions per 2 new states
+DEFINE_KERNEL(k_acs_pred, { const unsigned t = imad(a[i], seed | 1u, c); const unsigned u = iadd3(Y, c, seed & 0u); bool p, q;
+                            a[i] = __vibmin_u16x2(t, u, &p, &q); if (p) b += 1u << i; if (q) b += 0x10000u << i; })
 
 typedef void (*kern_t)(unsigned*, unsigned);
 
@@ -80,6 +105,10 @@ int main() {
     RUN(k_viaddmin_u16x2, 1); RUN(k_viaddmin_s16x2, 1); RUN(k_vimin3_u16x2, 1); RUN(k_vadd2, 1);
     RUN(k_vabsdiff4, 1); RUN(k_vimin_vadd2, 2); RUN(k_vibmin_pred, 1); RUN(k_hadd2, 1); RUN(k_hmin2, 2);
     RUN(k_mix_imad_lop3, 1); RUN(k_mix_imad_viaddmin, 1); RUN(k_mix_hadd2_viaddmin, 1); RUN(k_mix_lop3_viaddmin, 1);
+    RUN(k_hset2, 1); RUN(k_mix_hset2_viaddmin, 1); RUN(k_mix_hset2_imad, 1); RUN(k_mix_hset2_hadd2, 1);
+    RUN(k_mix3_viaddmin_imad_hset2, 1);
+    RUN(k_acs_fused_fma_t_alu_h, 4); RUN(k_acs_fused_alu_t_fma_h, 4); RUN(k_acs_fused_alu_t_alu_h, 4); RUN(k_acs_fused_fma_t_fma_h, 4);
+    RUN(k_acs_pred, 5);
     cudaFree(d_out);
     return 0;
 }
