@@ -4,6 +4,7 @@
 #include "kernels.h"
 #include "decision_layout.cuh"
 #include "acs_grp.cuh"
+#include "api_internal.h"
 
 #include <cstdarg>
 #include <cstdio>
@@ -122,6 +123,12 @@ static int fill_params(CodecParams& c, int codec, int K, int R, const int* poly,
         c.renorm_threshold = (int)wy->renormalisation_threshold;
     }
     return B200V_OK;
+}
+
+// the same two services for the library's other host files (api_internal.h)
+int b200v::api_fail(int code, const char* msg) { return fail(code, "%s", msg); }
+int b200v::api_fill_params(CodecParams& c, int codec, int K, int R, const int* poly, const b200v_wy_config* wy) {
+    return fill_params(c, codec, K, R, poly, wy);
 }
 
 // ---------------------------------------------------------------------------------------------------

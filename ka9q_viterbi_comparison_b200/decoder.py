@@ -86,6 +86,8 @@ def load_library():
         "b200v_batch_chainback_best_dev": (i32, [vp, vp, sz, u32, vp]),
         "b200v_batch_decode": (i32, [vp, vp, vp, u32]),
         "b200v_batch_decode_dev": (i32, [vp, vp, sz, vp, sz, u32]),
+        "b200v_decode_noalloc_dev": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(WyConfig), i32, i32, vp, sz, vp, sz, u32,
+                                           i32, vp]),
         "b200v_batch_sync": (i32, [vp]),
         "b200v_batch_get_decisions": (i32, [vp, i32, i32, i32, vp]),
         "b200v_batch_get_metrics": (i32, [vp, i32, vp]),
@@ -123,7 +125,7 @@ EXPORTED_SYMBOLS = [
     "b200v_codec_symbol_bytes", "b200v_codec_metric_bytes", "b200v_batch_create", "b200v_batch_destroy",
     "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_set_traceback", "b200v_batch_init",
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
-    "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_batch_sync", "b200v_batch_get_decisions",
+    "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_decode_noalloc_dev", "b200v_batch_sync", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
     "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_shard_range", "b200v_sharded_create",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
@@ -303,6 +305,25 @@ class BatchDecoder:
 
     def __exit__(self, *exc):
         self.close()
+
+
+NOALLOC_SCRATCH_BYTES = 32 << 20     # B200V_NOALLOC_SCRATCH_BYTES
+
+
+def decode_noalloc_dev(codec, frame_steps, n_frames, d_syms, sym_stride, d_out, out_stride, nbits, K=0, R=0, poly=None,
+                       device=0, cuda_stream=None, wy_config=None):
+    """b200v_decode_noalloc_dev: init + update + chainback of a K=7 batch with device buffers and no device allocation
+    (scratch in a static __device__ array of the library). Asynchronous on ``cuda_stream`` (None = default stream)."""
+    lib = load_library()
+    if isinstance(codec, str):
+        codec = CODEC_BY_NAME[codec]
+    k, r = C.c_int(0), C.c_int(0)
+    _check(lib.b200v_codec_shape(codec, C.byref(k), C.byref(r)))
+    K, R = k.value or K, r.value or R
+    poly = list(poly if poly is not None else STANDARD_POLYS[(K, R)])
+    cfg = C.byref(wy_config) if wy_config is not None else None
+    _check(lib.b200v_decode_noalloc_dev(codec, K, R, (C.c_int * len(poly))(*poly), cfg, frame_steps, n_frames,
+                                        _ptr(d_syms), sym_stride, _ptr(d_out), out_stride, nbits, device, cuda_stream))
 
 
 def shard_range(n_frames, n_shards, shard):
