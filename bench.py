@@ -375,6 +375,8 @@ def parity_sample(w, dec, d_syms, d_out, srow, orow, T, n_sample):
         n_sample = min(n_sample, 2)
     frames, nbits = w["frames"], w["frame_bits"]
     idx = sorted(set(int(round(x)) for x in np.linspace(0, frames - 1, min(n_sample, frames))))
+    if not idx:          # --parity-frames 0 (profiler runs)
+        return {"frames": 0, "mismatches": 0, "decision_frames": 0, "decision_mismatches": 0}
     with_decisions = set(idx[:: max(1, len(idx) // 3)][:3] + [idx[-1]])
     chk = o.Ref(name, T) if use_ref else o.Oracle(c, T)
     sdt = o.sym_dtype(c)

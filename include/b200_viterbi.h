@@ -161,8 +161,7 @@ int b200v_batch_decode_dev(b200v_batch* h, const void* d_syms, size_t sym_stride
  * in one static __device__ array of B200V_NOALLOC_SCRATCH_BYTES inside the library (held by every GPU that loads it,
  * until exit). Calls no cudaMalloc / cudaFree / allocating routine. Serves the K=7 codecs of the register kernel with
  * 8-bit symbols (KA9Q27, SPIRAL27, SPIRAL47, WY_U8 with a K=7 polynomial set it is instantiated for); the batch must fit:
- *   round256(steps) + round256(4*(ceil(n_frames/128)+1)) + round256(128*n_frames) + 8*steps*n_frames
- *                                                             <= B200V_NOALLOC_SCRATCH_BYTES
+ *   round256(steps) + round256(128*n_frames) + 8*steps*n_frames <= B200V_NOALLOC_SCRATCH_BYTES
  * (e.g. 2026 frames x 2054 steps, or 510 x 8198); larger batches are rejected with B200V_ERR_ARG and a message.
  * d_syms / d_data are device pointers laid out as for b200v_batch_decode_dev; cuda_stream is a cudaStream_t (NULL = the
  * default stream). Asynchronous on that stream. Every call on a GPU shares the one array: calls that overlap on the GPU

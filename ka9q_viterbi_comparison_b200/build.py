@@ -5,7 +5,8 @@ import subprocess
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.path.join(PKG_DIR, "libb200viterbi.so")
+# B200V_LIB: load another build of the library instead (A/B measurements of kernel variants; see tools/build_variant.py)
+LIB_PATH = os.environ.get("B200V_LIB") or os.path.join(PKG_DIR, "libb200viterbi.so")
 # the reference's per-codec C++ API on top of the C-ABI (include/ref_compat/): a separate library so that its
 # C++-linkage symbols never meet the reference's own objects in one link
 COMPAT_SRC = os.path.join(CSRC, "ref_compat.cpp")

@@ -25,6 +25,8 @@
 #include "dpx.cuh"
 #include "policy.cuh"
 
+#include <type_traits>
+
 namespace b200v {
 namespace grp {
 
@@ -72,7 +74,20 @@ struct Cfg {
     static constexpr int TOP = (s16 || POLICY == P_WY_U16) ? 65535 : 255;
     static constexpr int SB = (POLICY == P_WY_U16) ? 2 : 1;     // bytes per input symbol
     // rebase the lanes when their minimum exceeds TH: window = TH + metric spread + two branch metrics < 2^16
-    static constexpr unsigned TH = (TOP == 65535) ? 4096u : 16384u;
+    // mask decisions (dpx.cuh): compare-select as one VIADDMNMX, decision read back with HSET2 -- needs every lane inside
+    // [0, 0x7c00]. The modular policy always uses them (ka9q29 update 15.7 -> 14.3 ms per 256 Ki frames together with the
+    // unguarded whole groups of the main loop). For the SATURATING policies the form exists (GRP_MASK_SAT=1, bit-exact:
+    // 8-bit policies: lanes <= TH + 255 + two branch metrics; ka9q s16: TH + (skip + 1) branch metrics + spread
+    // (K-1) * 1530 + one candidate, fits with TH = 512 and at most three deferred steps; wy-u16 does not fit) but it
+    // measured SLOWER: the clamp add, the fused select and the HSET2 are three ALU-pipe instructions per register where
+    // the predicate form has two (its decisions are predicated FADDs on the otherwise idle FMA-lite pipe) --
+    // spiral29 18.8 -> 20.9 ms, wy-u8 K9R2 19.9 -> 22.2, ka9q615 37.0 -> 43.7, spiral615 43.4 -> 47.2 (profiles/r02_ab_mask_sat.txt).
+#ifndef GRP_MASK_SAT
+#define GRP_MASK_SAT 0
+#endif
+    static constexpr bool MASK = modular || (GRP_MASK_SAT && POLICY != P_WY_U16);
+    static constexpr int WINDOW = MASK ? 0x7c00 : 65535;
+    static constexpr unsigned TH = (TOP == 65535) ? ((MASK && s16) ? 512u : 4096u) : 16384u;
     // 16-bit policies trigger their renormalisation rarely (threshold >> one branch metric): after a checked step
     // the next `skip` steps provably cannot trigger (state 0 gains at most one branch metric per step), so those
     // steps run without the frame-wide minimum and its barrier. Block-uniform only when a frame owns the block.
@@ -98,7 +113,7 @@ struct GrpArgs {
     int frame0, count;             // frames [frame0, frame0 + count) of the n_frames-wide layout
     int C, thr, soft_hi, soft_lo;
     int one;                       // 1 (a multiplier ptxas cannot fold: keeps the lo-path adds on the FMA pipe)
-    int zero;                      // 0 (a third add operand ptxas cannot fold: keeps an add on the ALU pipe as IADD3)
+    int two;                       // 2 (multiplier of the decision fold, opaque to ptxas: keeps it an IMAD on the FMA pipe)
 };
 
 // symbol i of a step (u8 for ka9q/spiral, int8 / int16 for the williamyang policies)
@@ -223,7 +238,7 @@ struct FrameState {
 
 template <int POLICY, class CF>
 __device__ __forceinline__ void set_clamp(FrameState& fs, int bm_max) {
-    const int c = min(CF::TOP - fs.base, 65535 - bm_max);
+    const int c = min(CF::TOP - fs.base, CF::WINDOW - bm_max);
     fs.clamp = (uint32_t)c * 0x10001u;
 }
 
@@ -257,41 +272,111 @@ __device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint
 // the FMA pipe (IMAD), and the decisions are accumulated with predicated FADDs (dpx.cuh: min_facc).
 struct DecAcc { float al, ah, bl, bh; };
 
+// Where a register pair finds its packed branch metrics {W, Wc} of (static) code word c:
+//  * TabLds: one LDS.64 from the step's shared-memory table at entry c ^ (the thread's own code-word contribution);
+//  * TabReg (step tables of four entries, r = 1/2): the thread fetches its permutation of the whole table once per step
+//    (4 LDS.64) and every pair reads registers: 12 LDS.64 and 12 address LOP3s fewer per step.
+struct TabLds {
+    uint32_t A;
+    template <unsigned C> __device__ __forceinline__ void get(uint32_t& W, uint32_t& Wc) const { lds64(A ^ (C << 3), W, Wc); }
+};
+struct TabReg {
+    uint32_t W[4], Wc[4];
+    __device__ __forceinline__ explicit TabReg(uint32_t A) {
+#pragma unroll
+        for (unsigned c = 0; c < 4; c++) lds64(A ^ (c << 3), W[c], Wc[c]);
+    }
+    template <unsigned C> __device__ __forceinline__ void get(uint32_t& w, uint32_t& wc) const { w = W[C]; wc = Wc[C]; }
+};
+
 template <int POLICY, class CODE, int P, int KK>
 struct PairLoop {
-    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], uint32_t A, uint32_t clamp, uint32_t one, DecAcc& d) {
+    template <class TAB>
+    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], const TAB& tab, uint32_t clamp, uint32_t one, DecAcc& d) {
         constexpr int NXB = CODE::K - 1 - NL;
         constexpr int XB = NL - 1 - P;
         constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
         constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
-        if constexpr (POLICY == P_KA9Q_U8_MOD) {
-            // ka9q modular policy (viterbi29_sse2.cpp:137-158): the lanes hold the UNWRAPPED metric U (reference
-            // metric = U mod 256; the kernel prologue unwraps around state 0). The reference relies on the metric
-            // spread staying below 128, so its (int8)(m0 - m1) > 0 is the plain U compare: survivor = min,
-            // decision = (lo path > hi path), tie -> 0. No saturation, no renormalisation: four plain adds (two on
-            // each pipe), two packed mins, predicated FADD decisions.
-            uint32_t W, Wc;
-            lds64(A ^ (c << 3), W, Wc);
-            const uint32_t m0 = add_fma(w[iA], one, W), m1 = add_alu(w[iB], Wc, clamp);
-            const uint32_t m2 = add_fma(w[iA], one, Wc), m3 = add_alu(w[iB], W, clamp);
-            w[iA] = min_facc_strict<KK>(m0, m1, d.al, d.ah);
-            w[iB] = min_facc_strict<KK>(m2, m3, d.bl, d.bh);
-            PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, one, d);
-            return;
-        }
         uint32_t W, Wc;
-        lds64(A ^ (c << 3), W, Wc);
+        tab.template get<c>(W, Wc);
         const uint32_t m0 = add_fma(w[iA], one, W), m1 = __viaddmin_u16x2(w[iB], Wc, clamp);
         const uint32_t m2 = add_fma(w[iA], one, Wc), m3 = __viaddmin_u16x2(w[iB], W, clamp);
         // decision = (min == hi path): tie -> 1 (viterbi615_sse2.cpp:145-148, spiral615.cpp:247-250, sse_u8.h:111-114)
         w[iA] = min_facc<KK>(m1, m0, d.al, d.ah);
         w[iB] = min_facc<KK>(m3, m2, d.bl, d.bh);
-        PairLoop<POLICY, CODE, P, KK + 1>::run(w, A, clamp, one, d);
+        PairLoop<POLICY, CODE, P, KK + 1>::run(w, tab, clamp, one, d);
     }
 };
 template <int POLICY, class CODE, int P>
 struct PairLoop<POLICY, CODE, P, 16> {
-    __device__ __forceinline__ static void run(uint32_t (&)[NREG], uint32_t, uint32_t, uint32_t, DecAcc&) {}
+    template <class TAB>
+    __device__ __forceinline__ static void run(uint32_t (&)[NREG], const TAB&, uint32_t, uint32_t, DecAcc&) {}
+};
+
+// ka9q modular policy (viterbi29_sse2.cpp:137-158), mask decisions (dpx.cuh): the lanes hold the UNWRAPPED metric U
+// (reference metric = U mod 256; the kernel prologue unwraps around state 0; the spread stays below 128 -- bound in the
+// file header of acs_k7.cu and tests/test_oracle.py -- so the reference's (int8)(m0 - m1) > 0 is the plain U compare):
+// survivor = min, decision = (lo path > hi path), tie -> 0 = (survivor != lo path). No saturation, no renormalisation.
+// Per register: plain add (lo path), VIADDMNMX (min with hi path + metric), HSET2 (lane mask), IMAD (fold): with the table
+// fetch 10 instructions per register pair instead of 12, and no predicates. KK runs 15 ... 0 so that register pair KK
+// lands at bit KK / 16 + KK of the folded words (the layout of acs_grp.cuh). Window note: U < 512 + 128 + 1280 * 15 + 15
+// between the rebases (every 256 groups), inside [0, 0x7c00].
+template <int POLICY, class CODE, int P, int KK>
+struct PairLoopM {
+    template <class TAB>
+    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], const TAB& tab, uint32_t two, uint32_t& h0, uint32_t& h1) {
+        constexpr int NXB = CODE::K - 1 - NL;
+        constexpr int XB = NL - 1 - P;
+        constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
+        constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
+        uint32_t W, Wc;
+        tab.template get<c>(W, Wc);
+        const uint32_t t0 = w[iA] + W;
+        const uint32_t n0 = __viaddmin_u16x2(w[iB], Wc, t0);
+        h0 = horner_mask(h0, two, ne_mask_u16x2(n0, t0));
+        const uint32_t t1 = w[iA] + Wc;
+        const uint32_t n1 = __viaddmin_u16x2(w[iB], W, t1);
+        h1 = horner_mask(h1, two, ne_mask_u16x2(n1, t1));
+        w[iA] = n0;
+        w[iB] = n1;
+        PairLoopM<POLICY, CODE, P, KK - 1>::run(w, tab, two, h0, h1);
+    }
+};
+template <int POLICY, class CODE, int P>
+struct PairLoopM<POLICY, CODE, P, -1> {
+    template <class TAB>
+    __device__ __forceinline__ static void run(uint32_t (&)[NREG], const TAB&, uint32_t, uint32_t&, uint32_t&) {}
+};
+
+// saturating policies, mask decisions: hi path with the saturating clamp, survivor = min(lo + metric, hi path) as the second
+// VIADDMNMX, decision = (survivor == hi path): tie -> 1 (viterbi615_sse2.cpp:145-148, spiral615.cpp:247-250,
+// sse_u8.h:111-114), also when both paths saturate (the hi path then equals the clamp and the lo path exceeds it).
+template <int POLICY, class CODE, int P, int KK>
+struct PairLoopS {
+    template <class TAB>
+    __device__ __forceinline__ static void run(uint32_t (&w)[NREG], const TAB& tab, uint32_t clamp, uint32_t two,
+                                               uint32_t& h0, uint32_t& h1) {
+        constexpr int NXB = CODE::K - 1 - NL;
+        constexpr int XB = NL - 1 - P;
+        constexpr int iA = k7::expand_bit(KK, XB), iB = iA | (1 << XB);
+        constexpr unsigned c = CODE::cw2(state_of(NXB, P, iA, 0) << 1);
+        uint32_t W, Wc;
+        tab.template get<c>(W, Wc);
+        const uint32_t m1 = __viaddmin_u16x2(w[iB], Wc, clamp);
+        const uint32_t n0 = __viaddmin_u16x2(w[iA], W, m1);
+        h0 = horner_mask(h0, two, eq_mask_u16x2(n0, m1));
+        const uint32_t m3 = __viaddmin_u16x2(w[iB], W, clamp);
+        const uint32_t n1 = __viaddmin_u16x2(w[iA], Wc, m3);
+        h1 = horner_mask(h1, two, eq_mask_u16x2(n1, m3));
+        w[iA] = n0;
+        w[iB] = n1;
+        PairLoopS<POLICY, CODE, P, KK - 1>::run(w, tab, clamp, two, h0, h1);
+    }
+};
+template <int POLICY, class CODE, int P>
+struct PairLoopS<POLICY, CODE, P, -1> {
+    template <class TAB>
+    __device__ __forceinline__ static void run(uint32_t (&)[NREG], const TAB&, uint32_t, uint32_t, uint32_t&, uint32_t&) {}
 };
 
 // exchange after a whole group: phase-5 layout (register q, lane, tx) = state (2tx+lane)*32 + q  ->  shared
@@ -471,9 +556,24 @@ template <int POLICY, class CODE, class CF, int P, bool EXCH>
 __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const GrpArgs& a, uint32_t sub_addr,
                                      uint32_t cx8, unsigned long long* dec_out, bool live, uint32_t met_addr,
                                      uint32_t* s_red, int& rpar, int tid, int tx) {
-    DecAcc d = { FDEC_ZERO, FDEC_ZERO, FDEC_ZERO, FDEC_ZERO };
-    PairLoop<POLICY, CODE, P, 0>::run(w, sub_addr + cx8, fs.clamp, (uint32_t)a.one, d);
-    if (live) *dec_out = (unsigned long long)fdec_pack(d.al, d.ah) | ((unsigned long long)fdec_pack(d.bl, d.bh) << 32);
+#ifndef GRP_TABREG
+#define GRP_TABREG 1
+#endif
+    using TAB = typename std::conditional<(GRP_TABREG && CF::NCW == 4), TabReg, TabLds>::type;
+    const TAB tab{ sub_addr + cx8 };
+    if constexpr (CF::modular) {
+        uint32_t h0 = 0, h1 = 0;
+        PairLoopM<POLICY, CODE, P, 15>::run(w, tab, fs.clamp, h0, h1);     // modular policy: the clamp slot carries 2
+        if (live) *dec_out = (unsigned long long)horner_decode(h0) | ((unsigned long long)horner_decode(h1) << 32);
+    } else if constexpr (CF::MASK) {
+        uint32_t h0 = 0, h1 = 0;
+        PairLoopS<POLICY, CODE, P, 15>::run(w, tab, fs.clamp, (uint32_t)a.two, h0, h1);
+        if (live) *dec_out = (unsigned long long)horner_decode(h0) | ((unsigned long long)horner_decode(h1) << 32);
+    } else {
+        DecAcc d = { FDEC_ZERO, FDEC_ZERO, FDEC_ZERO, FDEC_ZERO };
+        PairLoop<POLICY, CODE, P, 0>::run(w, tab, fs.clamp, (uint32_t)a.one, d);
+        if (live) *dec_out = (unsigned long long)fdec_pack(d.al, d.ah) | ((unsigned long long)fdec_pack(d.bl, d.bh) << 32);
+    }
     if constexpr (CF::modular) {
         if (EXCH) {
             exchange_store<CF>(w, met_addr, tx);
@@ -521,8 +621,11 @@ __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const 
     renorm<POLICY, CF>(w, fs, gmin, g0, a);
 }
 
+#ifndef GRP_MINB
+#define GRP_MINB 4
+#endif
 template <int POLICY, class CODE>
-__global__ void __launch_bounds__((Cfg<POLICY, CODE>::THREADS), (Cfg<POLICY, CODE>::TPF >= 32 ? 3 : 4))
+__global__ void __launch_bounds__((Cfg<POLICY, CODE>::THREADS), (Cfg<POLICY, CODE>::TPF >= 32 ? 3 : GRP_MINB))
 acs_grp_kernel(const GrpArgs a) {
     using CF = Cfg<POLICY, CODE>;
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -565,11 +668,11 @@ acs_grp_kernel(const GrpArgs a) {
     }
     FrameState fs;
     fs.base = 0;
-    fs.clamp = CF::modular ? (uint32_t)a.zero : 0u;     // modular policy: no clamp; the slot carries add_alu's zero
+    fs.clamp = CF::modular ? (uint32_t)a.two : 0u;      // modular policy: no clamp; the slot carries the fold's multiplier 2
     fs.skip = 0;
     {   // min(w) <= TH + skip * bm_max between rebases; window: that + (K + 1) branch metrics of spread and headroom
         const int bmx = max(bm_cap<POLICY, CF::TOP>(a.C), 1);
-        fs.skip_cap = max(0, min(10, (65535 - (int)CF::TH - (CF::K + 1) * bmx) / bmx - 1));
+        fs.skip_cap = max(0, min(10, (CF::WINDOW - (int)CF::TH - (CF::K + 1) * bmx) / bmx - 1));
     }
     if (!CF::modular) {   // bring the lanes down to the bottom of the 16-bit window
         uint32_t gmin, g0;
@@ -600,8 +703,41 @@ acs_grp_kernel(const GrpArgs a) {
     if (ngroups > 0) fill_tables<POLICY, CODE, CF>(a, sp, 0, tab_addr, tx, fl);
     if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
 
+    // Whole groups run their five steps unconditionally: a step guarded by `if (nsub > s)` ends in a join where ptxas
+    // must bring the 32 renamed metric registers of the taken path back to the places of the skipped one (measured on
+    // ka9q29: 24 IMAD.MOV per step, 12 % of the instruction stream). Only the last, partial group keeps the guards.
+    const int nfull = a.nsteps / NL;
+    auto modular_rebase = [&](int g) {
+        if (CF::modular && (g & 255) == 255) {
+            // unwrapped lanes gain at most 15 per step: every 1280 steps bring them down by a multiple of 256
+            // (keeps U mod 256), leaving the minimum in [256, 512); the lanes stay inside the window of the mask compare
+            uint32_t gmin, g0;
+            frame_min<CF>(local_min(w), w[0], s_red, rpar, tid, gmin, g0);
+            const uint32_t sub = (gmin & ~255u) >= 256u ? (gmin & ~255u) - 256u : 0u;
+#pragma unroll
+            for (int i = 0; i < NREG; i++) w[i] -= sub * 0x10001u;
+        }
+    };
+#ifndef GRP_UNCOND_ALL
+#define GRP_UNCOND_ALL 0
+#endif
+    constexpr bool UNCOND = CF::modular || GRP_UNCOND_ALL;
+    const int nmain = UNCOND ? nfull : 0;
 #pragma unroll 1
-    for (int g = 0; g < ngroups; g++) {
+    for (int g = 0; g < nmain; g++) {
+        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx, fl);
+        const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
+        step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
+        step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);
+        step<POLICY, CODE, CF, 2, false>(w, fs, a, gt + 2 * CF::SUBTAB, cx8[2], drow + 2 * dstride, live, met_addr, s_red, rpar, tid, tx);
+        step<POLICY, CODE, CF, 3, false>(w, fs, a, gt + 3 * CF::SUBTAB, cx8[3], drow + 3 * dstride, live, met_addr, s_red, rpar, tid, tx);
+        step<POLICY, CODE, CF, 4, true>(w, fs, a, gt + 4 * CF::SUBTAB, cx8[4], drow + 4 * dstride, live, met_addr, s_red, rpar, tid, tx);
+        drow += NL * dstride;
+        modular_rebase(g);
+    }
+    // the last, partial group (and, for the kernels that measured slower with unguarded steps, every group)
+#pragma unroll 1
+    for (int g = nmain; g < ngroups; g++) {
         const int nsub = min(NL, a.nsteps - g * NL);
         if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx, fl);
         const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
@@ -611,15 +747,7 @@ acs_grp_kernel(const GrpArgs a) {
         if (nsub > 3) step<POLICY, CODE, CF, 3, false>(w, fs, a, gt + 3 * CF::SUBTAB, cx8[3], drow + 3 * dstride, live, met_addr, s_red, rpar, tid, tx);
         if (nsub > 4) step<POLICY, CODE, CF, 4, true>(w, fs, a, gt + 4 * CF::SUBTAB, cx8[4], drow + 4 * dstride, live, met_addr, s_red, rpar, tid, tx);
         drow += NL * dstride;
-        if (CF::modular && (g & 511) == 511) {
-            // unwrapped lanes gain at most 15 per step: every 2560 steps bring them down by a multiple of 256
-            // (keeps U mod 256), leaving the minimum in [256, 512)
-            uint32_t gmin, g0;
-            frame_min<CF>(local_min(w), w[0], s_red, rpar, tid, gmin, g0);
-            const uint32_t sub = (gmin & ~255u) >= 256u ? (gmin & ~255u) - 256u : 0u;
-#pragma unroll
-            for (int i = 0; i < NREG; i++) w[i] -= sub * 0x10001u;
-        }
+        modular_rebase(g);
     }
 
     // ---- registers (phase pf layout) -> canonical metrics, through shared memory ----
@@ -723,7 +851,7 @@ cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_st
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;
-    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1; a.zero = 0;
+    a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.one = 1; a.two = 2;
     switch (grp::find_instance(c)) {
     case grp::I_WY8_IS95: return grp::launch_one<P_WY_U8, grp::CodeIS95>(a, st);
     case grp::I_WY16_IS95: return grp::launch_one<P_WY_U16, grp::CodeIS95>(a, st);

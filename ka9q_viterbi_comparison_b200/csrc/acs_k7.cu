@@ -112,22 +112,8 @@ struct K7Args {
     int C, thr, soft_hi, soft_lo;
     int one, neg1;                 // 1 and -1, opaque to ptxas: multipliers that keep plain adds on the FMA pipe
     int zero;                      // 0, opaque to ptxas: third operand that keeps an add on the ALU pipe (IADD3)
-    unsigned* done;                // SIGNAL kernels: done[block] += 1 per warp once the block's decision rows are written
+    int two;                       // 2, opaque to ptxas: multiplier of the decision fold (keeps it an IMAD on the FMA pipe)
 };
-
-// Block-completion counter (release pattern: warp barrier, gpu-scope fence, relaxed atomic): lets a consumer on
-// another stream see which blocks' decision rows are in memory. Its other effect is the reason the ka9q27 instance
-// always uses it: with these few extra instructions ptxas allocates 72 registers WITHOUT spills (7 resident blocks
-// per SM, 28 warps) where the plain kernel takes 78 (6 blocks) and __launch_bounds__(128, 7) spills 116 bytes
-// (45 ms): 15.90 -> 14.04 ms per 1 Mi frames, bit-identical output (profiles/r01d_k7_signal_variant.txt).
-
-__device__ __forceinline__ void signal_done(unsigned* done) {
-    __syncwarp(__activemask());
-    if ((threadIdx.x & 31) == 0) {
-        __threadfence();
-        atomicAdd(done + blockIdx.x, 1u);
-    }
-}
 
 // ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
 template <int POLICY, class CODE, int P, int KK>
@@ -180,6 +166,64 @@ struct PairLoop<POLICY, CODE, P, 16> {
                                                const K7Args&, uint32_t&, uint32_t&) {}
 };
 
+// ---- mask-decision form of the same butterflies (dpx.cuh, "mask decisions") ------------------------------------------
+// Per register of two new states: 1 add (lo-path candidate t), 1 VIADDMNMX (n = min(hi + metric, t)), 1 HSET2 (lane mask of
+// the decision), 1 IMAD (fold): 4 instructions where the predicate form needs 5 (2 adds, VIMNMX, 2 predicated ORs), and
+// no predicate registers. KK runs 15 ... 0 so that pair KK lands at bit KK / 16 + KK of the folded word (the bitwise
+// packing of acs_k7.cuh). Window note: the unwrapped lanes of the modular policy stay below 512 + 128 + 96 * 15 + 15
+// (rebased every 16 periods), far inside [0, 0x7c00].
+#ifndef K7_MASK_DECISIONS
+#define K7_MASK_DECISIONS 1
+#endif
+template <int POLICY, class CODE, int P, int KK>
+struct PairLoopM {
+    __device__ __forceinline__ static void run(uint32_t (&w)[NW], const uint32_t* W, const uint32_t* Wc,
+                                               const K7Args& a, uint32_t& h0, uint32_t& h1) {
+        constexpr int XB = NB - 2 - P;
+        constexpr int iA = expand_bit(KK, XB), iB = iA | (1 << XB);
+        constexpr int c = CODE::cw(logical_of(P, iA << 1));
+        const uint32_t A = w[iA], B = w[iB];
+        // decision = (lo path > hi path), tie -> 0 (viterbi27_sse2.cpp:155-158): the survivor differs from the lo path
+        // (measured on the 1 Mi-frame batch, update kernel: predicate form 14.05 ms; this form 13.09 ms with plain adds
+        // -- ptxas emits them as IMAD.IADD on the FMA pipe, which balances the two ALU instructions; forcing 8 or 16 of
+        // the adds or folds onto the ALU pipe costs 13.8 / 14.3 ms, __launch_bounds__(128, 7) spills: 13.7 ms)
+        const uint32_t t0 = A + W[c];
+        const uint32_t n0 = __viaddmin_u16x2(B, Wc[c], t0);
+        h0 = horner_mask(h0, (uint32_t)a.two, ne_mask_u16x2(n0, t0));
+        const uint32_t t1 = A + Wc[c];
+        const uint32_t n1 = __viaddmin_u16x2(B, W[c], t1);
+        h1 = horner_mask(h1, (uint32_t)a.two, ne_mask_u16x2(n1, t1));
+        w[iA] = n0;
+        w[iB] = n1;
+        PairLoopM<POLICY, CODE, P, KK - 1>::run(w, W, Wc, a, h0, h1);
+    }
+};
+template <int POLICY, class CODE, int P>
+struct PairLoopM<POLICY, CODE, P, -1> {
+    __device__ __forceinline__ static void run(uint32_t (&)[NW], const uint32_t*, const uint32_t*, const K7Args&,
+                                               uint32_t&, uint32_t&) {}
+};
+// last phase: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1]); BC[c] = (bm, cm), CB[c] = (cm, bm)
+template <int POLICY, class CODE, int I>
+struct InRegLoopM {
+    __device__ __forceinline__ static void run(uint32_t (&w)[NW], const uint32_t* BC, const uint32_t* CB,
+                                               const K7Args& a, uint32_t& h0, uint32_t& h1) {
+        constexpr int c = CODE::cw(I);
+        const uint32_t x = w[I];
+        const uint32_t t = __byte_perm(x, x, 0x1010) + BC[c];                          // (lo + bm, lo + cm)
+        const uint32_t n = __viaddmin_u16x2(__byte_perm(x, x, 0x3232), CB[c], t);      // min with (hi + cm, hi + bm)
+        uint32_t& h = (I < 16) ? h0 : h1;
+        h = horner_mask(h, (uint32_t)a.two, ne_mask_u16x2(n, t));
+        w[I] = n;
+        InRegLoopM<POLICY, CODE, I - 1>::run(w, BC, CB, a, h0, h1);
+    }
+};
+template <int POLICY, class CODE>
+struct InRegLoopM<POLICY, CODE, -1> {
+    __device__ __forceinline__ static void run(uint32_t (&)[NW], const uint32_t*, const uint32_t*, const K7Args&,
+                                               uint32_t&, uint32_t&) {}
+};
+
 // last phase: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
 template <int POLICY, class CODE, int I>
 struct InRegLoop {
@@ -230,7 +274,18 @@ __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7
             W[c] = bm[c] + bm[c ^ DELTA] * 65536u;
             Wc[c] = EXACT_COMPLEMENT ? (uint32_t)a.C * 0x10001u - W[c] : cm[c] + cm[c ^ DELTA] * 65536u;
         }
-        PairLoop<POLICY, CODE, P, 0>::run(w, W, Wc, clamp, a, acc0, acc1);
+        if constexpr (K7_MASK_DECISIONS && Arith<POLICY>::modular) {
+            PairLoopM<POLICY, CODE, P, 15>::run(w, W, Wc, a, acc0, acc1);
+            acc0 = horner_decode(acc0); acc1 = horner_decode(acc1);
+        } else {
+            PairLoop<POLICY, CODE, P, 0>::run(w, W, Wc, clamp, a, acc0, acc1);
+        }
+    } else if constexpr (K7_MASK_DECISIONS && Arith<POLICY>::modular) {
+        uint32_t BC[NCW], CB[NCW];
+#pragma unroll
+        for (int c = 0; c < NCW; c++) { BC[c] = pack2(bm[c], cm[c]); CB[c] = pack2(cm[c], bm[c]); }
+        InRegLoopM<POLICY, CODE, NW - 1>::run(w, BC, CB, a, acc0, acc1);
+        acc0 = horner_decode(acc0); acc1 = horner_decode(acc1);
     } else {
         // in-register butterflies: register i = (old[i], old[i+32]) -> (new[2i], new[2i+1])
         InRegLoop<POLICY, CODE, 0>::run(w, bm, cm, clamp, acc0, acc1);
@@ -296,8 +351,9 @@ __device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE
 }
 
 // (__launch_bounds__(128, 6) for the saturating policies -- 80 registers, 8-16 bytes of spills -- measured no faster:
-// spiral27 21.6 ms either way, spiral47 23.0 -> 23.7 ms.)
-template <int POLICY, class CODE, bool SIGNAL>
+// spiral27 21.6 ms either way, spiral47 23.0 -> 23.7 ms. Round 2: the group kernels' decision collection for these
+// policies -- VIMNMX with predicate outputs + predicated FADDs -- takes 127 registers here (4 resident blocks): 23.9 ms.)
+template <int POLICY, class CODE>
 __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     constexpr int R = CODE::R;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -305,10 +361,7 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     if (blockIdx.x == 0) {   // phase of every decision row this launch writes (read by chainback)
         for (int t = threadIdx.x; t < a.nsteps; t += blockDim.x) a.row_phase[a.step0 + t] = (uint8_t)(t % NB);
     }
-    if (idx >= a.count) {
-        if (SIGNAL) signal_done(a.done);
-        return;
-    }
+    if (idx >= a.count) return;
 
     // ---- load canonical metrics into the phase-0 layout: register i = states (2i, 2i+1) ----
     uint32_t w[NW];
@@ -402,8 +455,6 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
         if (rem > 4) { run_step<POLICY, CODE, 4>(w, tb, a, off, &d); drow[4 * dstride] = d; }
     }
 
-    if (SIGNAL) signal_done(a.done);
-
     // ---- store canonical metrics: logical state n sits at physical_of(rem, n) ----
     uint32_t tmp[NW];
 #pragma unroll
@@ -421,8 +472,7 @@ template <int POLICY, class CODE>
 static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
     const int threads = 128;
     const int blocks = (a.count + threads - 1) / threads;
-    if (a.done) acs_k7_kernel<POLICY, CODE, true><<<blocks, threads, 0, st>>>(a);
-    else acs_k7_kernel<POLICY, CODE, false><<<blocks, threads, 0, st>>>(a);
+    acs_k7_kernel<POLICY, CODE><<<blocks, threads, 0, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -475,15 +525,14 @@ bool k7_supported(const CodecParams& c) {
 
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st, unsigned* done) {
+                          int frame0, int count, cudaStream_t st) {
     if (count <= 0 || nsteps <= 0) return cudaSuccess;
     k7::K7Args a;
-    a.done = done;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;
     a.C = c.max_error; a.thr = c.renorm_threshold; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
-    a.one = 1; a.neg1 = -1; a.zero = 0;
+    a.one = 1; a.neg1 = -1; a.zero = 0; a.two = 2;
     switch (k7::find_instance(c)) {
     case 0: return k7::launch_one<P_KA9Q_U8_MOD, k7::CodeK7R2>(a, st);
     case 1: return k7::launch_one<P_SPIRAL_R2, k7::CodeK7R2>(a, st);

@@ -165,7 +165,6 @@ struct b200v_batch {
     K24GraphCache k24_graph;     // K=24: captured step loop of the last update call
     bool user_variant = false;   // set_variant() was called: no automatic family changes
     int tb_mode = 0, tb_warmup = 0;   // b200v_batch_set_traceback
-    unsigned* k7_done = nullptr;      // K=7 modular register kernel: per-block count of warps that finished an update launch
     // lazily allocated staging for the host-pointer entry points
     void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
     uint8_t* d_out_stage = nullptr; size_t out_stage_bytes = 0;
@@ -184,8 +183,6 @@ static void free_all(b200v_batch* h) {
     if (h->ev_c1) cudaEventDestroy(h->ev_c1);
     for (int i = 0; i < b200v_batch::NPIPE; i++) if (h->pipe[i]) cudaStreamDestroy(h->pipe[i]);
     if (h->ev_pipe) cudaEventDestroy(h->ev_pipe);
-    if (h->k7_done) cudaFree(h->k7_done);
-
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }
@@ -394,15 +391,8 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
         CUDA_TRY(launch_acs_smallk(a, st));
         h->launches++;
     } else if (h->variant == 2) {
-        // ka9q27: the kernel variant that counts finished warps per block is the one ptxas fits into 72 registers
-        // without spills (7 resident blocks per SM instead of 6 at 78 registers): 15.9 -> 14.0 ms per 1 Mi frames
-        if (!h->k7_done && c.policy == P_KA9Q_U8_MOD) {
-            const size_t nb = ((size_t)h->n_frames + 127) / 128 + 1;
-            CUDA_TRY(cudaMalloc(&h->k7_done, nb * sizeof(unsigned)));
-            CUDA_TRY(cudaMemsetAsync(h->k7_done, 0, nb * sizeof(unsigned), st));
-        }
         CUDA_TRY(launch_acs_k7(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
-                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, h->k7_done));
+                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
         h->launches++;
     } else {
         GenericArgs a{};

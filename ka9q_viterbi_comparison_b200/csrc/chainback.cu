@@ -221,7 +221,56 @@ __global__ void best_state_kernel(const CodecParams c, const uint16_t* metrics, 
     }
 }
 
+// ---- sliding-window traceback: one thread per stream walks the ring from the stream's end state ----
+template <int LAYOUT>
+__global__ void __launch_bounds__(128) stream_traceback_kernel(const StreamTracebackArgs s) {
+    __shared__ uint8_t tab[LAYOUT == DL_K7_INTERLEAVED ? k7::NB * k7::S : 1];
+    if (LAYOUT == DL_K7_INTERLEAVED) fill_k7_table(tab, s.a.c.policy);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= s.a.count) return;
+    const int f = s.a.frame0 + idx;
+    const ParReader<LAYOUT> rd(s.a, f, tab);
+    const unsigned K1 = (unsigned)(s.a.c.K - 1), W = s.ring_rows;
+    uint8_t* out = s.a.out + (size_t)f * s.a.out_stride;
+    unsigned st = (s.a.endstates ? s.a.endstates[f] : s.a.endstate) % (unsigned)s.a.c.S;
+    const unsigned long long e0 = s.first_bit, e1 = s.first_bit + s.a.nbits;     // emitted bits [e0, e1)
+    unsigned cur = 0;
+    auto emit = [&](unsigned long long b, unsigned k) {
+        if (b >= e1) return;
+        cur = (cur >> 1) | (k << 7);
+        if (((b - e0) & 7ull) == 0) { out[(b - e0) >> 3] = (uint8_t)cur; cur = 0; }
+    };
+    unsigned long long b = s.top_row + 1;           // one past the newest input bit known so far
+    if (s.state_bits)                                // bit j of the state = input bit of step top_row - j
+        for (unsigned j = 0; j < K1 && b > e0; j++) { b--; emit(b, (st >> j) & 1u); }
+    else
+        b = s.top_row + 1 - K1;
+    // row r decides input bit r - (K-1); the state before the walk step is the one after row r
+    unsigned long long r = s.top_row;
+    unsigned p = (unsigned)(r % W);
+    while (b > e0) {
+        b--;
+        const unsigned k = rd.bit(p, st);
+        st = (st >> 1) | (k << (K1 - 1));
+        emit(b, k);
+        p = p == 0 ? W - 1 : p - 1;
+    }
+}
+
 }  // namespace
+
+cudaError_t launch_stream_traceback(const StreamTracebackArgs& s, cudaStream_t st) {
+    if (s.a.count <= 0 || s.a.nbits == 0) return cudaSuccess;
+    const int threads = 128, blocks = (s.a.count + threads - 1) / threads;
+    switch (s.a.layout) {
+    case DL_BALLOT_FRAME_MAJOR: stream_traceback_kernel<DL_BALLOT_FRAME_MAJOR><<<blocks, threads, 0, st>>>(s); break;
+    case DL_K7_INTERLEAVED: stream_traceback_kernel<DL_K7_INTERLEAVED><<<blocks, threads, 0, st>>>(s); break;
+    case DL_GRP_INTERLEAVED: stream_traceback_kernel<DL_GRP_INTERLEAVED><<<blocks, threads, 0, st>>>(s); break;
+    case DL_SMALLK_INTERLEAVED: stream_traceback_kernel<DL_SMALLK_INTERLEAVED><<<blocks, threads, 0, st>>>(s); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
 
 cudaError_t launch_best_state(const CodecParams& c, const uint16_t* metrics, unsigned* best, int n_frames, cudaStream_t st) {
     if (n_frames <= 0) return cudaSuccess;

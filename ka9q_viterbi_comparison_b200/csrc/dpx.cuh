@@ -86,6 +86,33 @@ __device__ __forceinline__ uint32_t sign_bytes(uint32_t x0, uint32_t x1) {
     asm("prmt.b32 %0, %1, %2, 0xfdb9;" : "=r"(d) : "r"(x0), "r"(x1));
     return d;
 }
+// ---- mask decisions (round 2): compare-select fused into one VIADDMNMX, decision read back as a lane mask --------------
+// n = min(hi + Wc, t) is ONE VIADDMNMX.U16x2 when t (the lo-path candidate) is its third operand; the decision of a lane
+// is then (n != t) [tie -> 0 policies] or (n == hi-path candidate) [tie -> 1 policies]. HSET2 compares the two u16 lanes
+// of its operands as f16 values and writes 0xffff / 0x0000 per lane: for lane values in [0, 0x7c00] (every bit pattern
+// there is a distinct, non-NaN f16 -- subnormals included, the instruction does not flush them) float equality IS
+// integer equality. The kernels keep their lanes inside that window (see each kernel's window note).
+__device__ __forceinline__ uint32_t ne_mask_u16x2(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("set.ne.u32.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t eq_mask_u16x2(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("set.eq.u32.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+// Sixteen lane masks m_15 ... m_0 (in that order) are folded into one word with h = 2 h + m on the FMA pipe (IMAD; `two`
+// is a register holding 2 that ptxas cannot fold). Per lane 0xffff = -1 (mod 2^16), so h = -(DL + 2^16 (DH - DL)) with
+// DL / DH the 16-bit words of lane-0 / lane-1 decisions (bit k = mask k); one multiply undoes the lane interplay and the
+// sign:  DL | DH << 16 = h * -(2^16 + 1)  (mod 2^32).
+__device__ __forceinline__ uint32_t horner_mask(uint32_t h, uint32_t two, uint32_t m) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(h), "r"(two), "r"(m));
+    return d;
+}
+__device__ __forceinline__ uint32_t horner_decode(uint32_t h) { return h * 0xFFFEFFFFu; }
+
 // a + b on the ALU pipe: a three-input add with an opaque zero stays an IADD3 (ptxas turns two-input adds into
 // VIADD / IMAD.IADD, both of which ncu attributes to the FMA-heavy pipe on B200)
 __device__ __forceinline__ uint32_t add_alu(uint32_t a, uint32_t b, uint32_t zero) {

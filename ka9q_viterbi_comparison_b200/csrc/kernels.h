@@ -41,7 +41,7 @@ cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecPara
 bool k7_supported(const CodecParams& c);
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st, unsigned* done = nullptr);
+                          int frame0, int count, cudaStream_t st);
 
 // ---- group kernels for K=9 / K=15 (acs_grp.cu): decisions as one u64 per (row, frame, thread of the frame) ----
 bool grp_supported(const CodecParams& c);
@@ -84,6 +84,21 @@ struct ChainbackArgs {
     int par_mode, par_warmup;   // b200v_batch_set_traceback: 0 auto / 1 per-frame threads / 2 block-parallel; warm-up rows or 0
 };
 cudaError_t launch_chainback(const ChainbackArgs& a, cudaStream_t st);
+// ---- sliding-window traceback over a ring of decision rows (chainback.cu) ----
+// Logical row r (the trellis step counted since init) lives at ring position r % ring_rows. Every stream is walked from
+// its end state (a.endstates[f], or a.endstate) at logical row top_row down to the row of the first emitted bit;
+// the bits [first_bit, first_bit + a.nbits) are written MSB-first to a.out + f * a.out_stride (bit first_bit = bit 7 of
+// byte 0). state_bits: the K-1 newest input bits [top_row + 2 - K, top_row] are read from the end state itself (best-state
+// flush of an unterminated stream); otherwise the newest bit a walk can produce is top_row - (K-1).
+struct StreamTracebackArgs {
+    ChainbackArgs a;            // decision layout / buffers (dec_rows = ring_rows), output, end states; a.nbits = bits emitted
+    unsigned ring_rows;
+    unsigned long long top_row; // newest row written (logical)
+    unsigned long long first_bit;
+    int state_bits;
+};
+cudaError_t launch_stream_traceback(const StreamTracebackArgs& s, cudaStream_t st);
+
 // best[f] = index of the smallest path metric of frame f (ties: lowest state); ka9q modular metrics are compared
 // as (int8) distances from state 0, s16 metrics as signed values
 cudaError_t launch_best_state(const CodecParams& c, const uint16_t* metrics, unsigned* best, int n_frames, cudaStream_t st);

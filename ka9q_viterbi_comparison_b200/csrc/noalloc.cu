@@ -12,7 +12,7 @@
 // kernels receive. Device code (noalloc_clear_kernel) may name the array directly.
 //
 // All calls share the array and it keeps the last call's contents: the entry point clears what must start at zero
-// (row phases, block counters) and rewrites the metrics on every call; decision rows are fully rewritten by the
+// (the row phases) and rewrites the metrics on every call; decision rows are fully rewritten by the
 // update before the traceback reads them. Two calls that overlap on one GPU (different streams, or two host threads)
 // RACE on the scratch: serialise them.
 #include "../../include/b200_viterbi.h"
@@ -45,7 +45,7 @@ cudaError_t scratch_base(int device, unsigned char** base) {
     return cudaSuccess;
 }
 
-// what must start at zero: the row phases and the per-block completion counters at the head of the array
+// what must start at zero: the row phases at the head of the array
 __global__ void noalloc_clear_kernel(size_t bytes) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < bytes / 16; i += (size_t)gridDim.x * blockDim.x)
         reinterpret_cast<uint4*>(g_scratch)[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -91,15 +91,14 @@ extern "C" int b200v_decode_noalloc_dev(int codec, int K, int R, const int* poly
     if (n_frames > 1 && sym_stride_bytes < (size_t)frame_steps * c.R)
         return failf(B200V_ERR_ARG, "frame stride %lld smaller than one frame's symbols", (long long)sym_stride_bytes);
 
-    // carve the array: [row phases][block counters] (cleared) [metrics][decision rows] (rewritten)
+    // carve the array: [row phases] (cleared) [metrics][decision rows] (rewritten)
     const size_t phase_bytes = round256((size_t)nsteps);
-    const size_t done_bytes = round256((((size_t)n_frames + 127) / 128 + 1) * sizeof(unsigned));
     const size_t metric_bytes = round256((size_t)n_frames * c.S * sizeof(uint16_t));
     const size_t dec_bytes = (size_t)nsteps * n_frames * sizeof(unsigned long long);
-    const size_t need = phase_bytes + done_bytes + metric_bytes + dec_bytes;
+    const size_t need = phase_bytes + metric_bytes + dec_bytes;
     if (need > (size_t)B200V_NOALLOC_SCRATCH_BYTES)
         return failf(B200V_ERR_ARG, "%lld frames of %lld steps need %lld bytes of scratch; the allocation-free entry point "
-                     "holds B200V_NOALLOC_SCRATCH_BYTES = 32 MiB (about frames * (steps * 8 + 132) bytes): use b200v_batch_*",
+                     "holds B200V_NOALLOC_SCRATCH_BYTES = 32 MiB (about frames * (steps * 8 + 128) bytes): use b200v_batch_*",
                      n_frames, nsteps, (long long)need);
 
     NA_TRY(cudaSetDevice(device));
@@ -107,16 +106,14 @@ extern "C" int b200v_decode_noalloc_dev(int codec, int K, int R, const int* poly
     NA_TRY(scratch_base(device, &base));
     cudaStream_t st = (cudaStream_t)cuda_stream;
     uint8_t* row_phase = base;
-    unsigned* done = reinterpret_cast<unsigned*>(base + phase_bytes);
-    uint16_t* metrics = reinterpret_cast<uint16_t*>(base + phase_bytes + done_bytes);
-    unsigned long long* dec = reinterpret_cast<unsigned long long*>(base + phase_bytes + done_bytes + metric_bytes);
+    uint16_t* metrics = reinterpret_cast<uint16_t*>(base + phase_bytes);
+    unsigned long long* dec = reinterpret_cast<unsigned long long*>(base + phase_bytes + metric_bytes);
 
-    const size_t clear = phase_bytes + done_bytes;
+    const size_t clear = phase_bytes;
     noalloc_clear_kernel<<<(unsigned)((clear / 16 + 255) / 256), 256, 0, st>>>(clear);
     NA_TRY(cudaGetLastError());
     NA_TRY(launch_init_metrics(metrics, n_frames, c, 0, st));
-    NA_TRY(launch_acs_k7(c, d_syms, sym_stride_bytes, nsteps, 0, dec, row_phase, metrics, n_frames, 0, n_frames, st,
-                         c.policy == P_KA9Q_U8_MOD ? done : nullptr));
+    NA_TRY(launch_acs_k7(c, d_syms, sym_stride_bytes, nsteps, 0, dec, row_phase, metrics, n_frames, 0, n_frames, st));
     ChainbackArgs a{};
     a.c = c; a.layout = DL_K7_INTERLEAVED; a.dec = dec; a.dec_rows = nsteps; a.row_words = 2;
     a.row_phase = row_phase; a.n_frames = n_frames; a.frame0 = 0; a.count = n_frames;

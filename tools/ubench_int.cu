@@ -71,6 +71,27 @@ DEFINE_KERNEL(k_acs_fused_fma_t_fma_h, ACS_FUSED(imad(a[i], seed | 1u, c), imad(
 DEFINE_KERNEL(k_acs_pred, { const unsigned t = imad(a[i], seed | 1u, c); const unsigned u = iadd3(Y, c, seed & 0u); bool p, q;
                             a[i] = __vibmin_u16x2(t, u, &p, &q); if (p) b += 1u << i; if (q) b += 0x10000u << i; })
 
+// ---- round 2b: is there a third pipe? HFMA2 / FFMA beside IMAD (FMA heavy) and the DPX ops (ALU) -------------------------
+__device__ __forceinline__ unsigned hfma2u(unsigned a, unsigned b, unsigned c) { unsigned d; asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+__device__ __forceinline__ unsigned ffmau(unsigned a, unsigned b, unsigned c) { return __float_as_uint(fmaf(__uint_as_float(a), __uint_as_float(b), __uint_as_float(c))); }
+__device__ __forceinline__ unsigned hne2h(unsigned a, unsigned b) { unsigned d; asm("set.ne.f16x2.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+DEFINE_KERNEL(k_hfma2, a[i] = hfma2u(a[i], c, Y))
+DEFINE_KERNEL(k_ffma, a[i] = ffmau(a[i], c, Y))
+DEFINE_KERNEL(k_mix_hfma2_imad, { if (i & 1) a[i] = hfma2u(a[i], c, Y); else a[i] = imad(a[i], b, Y); })
+DEFINE_KERNEL(k_mix_ffma_imad, { if (i & 1) a[i] = ffmau(a[i], c, Y); else a[i] = imad(a[i], b, Y); })
+DEFINE_KERNEL(k_mix_ffma_hfma2, { if (i & 1) a[i] = ffmau(a[i], c, Y); else a[i] = hfma2u(a[i], c, Y); })
+DEFINE_KERNEL(k_mix_ffma_viaddmin, { if (i & 1) a[i] = ffmau(a[i], c, Y); else a[i] = __viaddmin_u16x2(a[i], Y, c); })
+DEFINE_KERNEL(k_mix4_2viaddmin_imad_hfma2, { if ((i & 3) == 0) a[i] = imad(a[i], b, Y); else if ((i & 3) == 2) a[i] = hfma2u(a[i], c, Y); else a[i] = __viaddmin_u16x2(a[i], Y, c); })
+DEFINE_KERNEL(k_mix4_2viaddmin_imad_ffma, { if ((i & 3) == 0) a[i] = imad(a[i], b, Y); else if ((i & 3) == 2) a[i] = ffmau(a[i], c, Y); else a[i] = __viaddmin_u16x2(a[i], Y, c); })
+// fused ACS body with the fold on HFMA2: mask as f16 1.0 / 0.0, h = 2 h + m exact below 2^11
+#define ACS_FUSED_H(ADD_T)                                                                  \
+    { const unsigned t = ADD_T; const unsigned n = __viaddmin_u16x2(Y, c, t); const unsigned m = hne2h(n, t); \
+      b = hfma2u(b, 0x40004000u, m); a[i] = n; }
+DEFINE_KERNEL(k_acs_fused_fma_t_hfma2_h, ACS_FUSED_H(imad(a[i], seed | 1u, c)))
+DEFINE_KERNEL(k_acs_fused_alu_t_hfma2_h, ACS_FUSED_H(iadd3(a[i], c, seed & 0u)))
+DEFINE_KERNEL(k_acs_fused_add_t_hfma2_h, ACS_FUSED_H(a[i] + c))
+DEFINE_KERNEL(k_acs_fused_add_t_fma_h, ACS_FUSED(a[i] + c, imad(b, 2u + (seed & 0u), m)))
+
 typedef void (*kern_t)(unsigned*, unsigned);
 
 static void run(const char* name, kern_t k, unsigned* d_out, int sms, double clk_ghz, double ops_per_body) {
@@ -109,6 +130,10 @@ int main() {
     RUN(k_mix3_viaddmin_imad_hset2, 1);
     RUN(k_acs_fused_fma_t_alu_h, 4); RUN(k_acs_fused_alu_t_fma_h, 4); RUN(k_acs_fused_alu_t_alu_h, 4); RUN(k_acs_fused_fma_t_fma_h, 4);
     RUN(k_acs_pred, 5);
+    RUN(k_hfma2, 1); RUN(k_ffma, 1); RUN(k_mix_hfma2_imad, 1); RUN(k_mix_ffma_imad, 1); RUN(k_mix_ffma_hfma2, 1);
+    RUN(k_mix_ffma_viaddmin, 1); RUN(k_mix4_2viaddmin_imad_hfma2, 1); RUN(k_mix4_2viaddmin_imad_ffma, 1);
+    RUN(k_acs_fused_fma_t_hfma2_h, 4); RUN(k_acs_fused_alu_t_hfma2_h, 4); RUN(k_acs_fused_add_t_hfma2_h, 4);
+    RUN(k_acs_fused_add_t_fma_h, 4);
     cudaFree(d_out);
     return 0;
 }
