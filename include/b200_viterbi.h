@@ -174,6 +174,37 @@ int b200v_decode_noalloc_dev(int codec, int K, int R, const int* poly, const b20
 /* Wait for everything queued on the instance's stream. */
 int b200v_batch_sync(b200v_batch* h);
 
+/* ---- sliding-window decode of continuous streams ----
+ * The reference's decoders resume across update calls (viterbi27_sse2.cpp:121,174; sse_u8.h:59,67) and trace back over a
+ * configurable length (viterbi_decoder_core.h:180-189,214-236), but their decision storage is finite: an unbounded stream
+ * needs a window. b200v_stream keeps, for n_streams independent streams, a RING of depth + chunk decision rows:
+ *   push:  `chunk` more trellis steps per stream (metrics continue, as a resumed update), then every stream is traced back
+ *          from its own best state (smallest path metric, ties to the lowest state) through the ring, and the `chunk` oldest
+ *          input bits are emitted -- each with at least `depth` newer trellis steps behind it, the usual meaning of a
+ *          traceback depth. Push p (1-based) emits bits [p*chunk - depth - chunk, p*chunk - depth) once that range is
+ *          non-negative; earlier pushes emit nothing (*bits_out = 0).
+ *   flush: end of the stream: the remaining bits. endstate >= 0: the stream was tail-terminated into that state: emits bits
+ *          [emitted, steps - (K-1)) traced from it. endstate < 0: unterminated: traced from the best state, and the K-1
+ *          newest bits are the state itself: emits [emitted, steps).
+ * depth must be a multiple of chunk, chunk a multiple of 8 (and even: spiral codecs step in pairs), depth >= K-1.
+ * Bits are packed MSB-first, (bits+7)/8 bytes per stream at d_out + stream * out_stride_bytes; the first emitted bit of a
+ * call is bit 7 of byte 0. All codecs with K <= 16. Asynchronous on the instance's stream. */
+typedef struct b200v_stream b200v_stream;
+b200v_stream* b200v_stream_create(int codec, int K, int R, const int* poly, int n_streams, int depth, int chunk,
+                                  int device, const b200v_wy_config* wy_config);
+void b200v_stream_destroy(b200v_stream* s);
+/* init(starting_state) of every stream; forgets the window. */
+int b200v_stream_reset(b200v_stream* s, int starting_state);
+int b200v_stream_push_dev(b200v_stream* s, const void* d_syms, size_t sym_stride_bytes, uint8_t* d_out,
+                          size_t out_stride_bytes, unsigned* bits_out);
+int b200v_stream_flush_dev(b200v_stream* s, int endstate, uint8_t* d_out, size_t out_stride_bytes, unsigned* bits_out);
+/* trellis steps consumed / bits emitted per stream since the last reset */
+long long b200v_stream_steps(const b200v_stream* s);
+long long b200v_stream_emitted(const b200v_stream* s);
+int b200v_stream_sync(b200v_stream* s);
+/* the batch instance behind the stream (introspection: b200v_batch_get_metrics, b200v_batch_launch_count ...) */
+b200v_batch* b200v_stream_batch(b200v_stream* s);
+
 /* ---- introspection (parity tests, SURVEY 8b "b200v_batch_get_decisions") ---- */
 /* Canonical decision vectors of one frame: max(S/8, 1) bytes per step, bit n of the little-endian vector is the
  * decision of new state n (the layout every reference decoder uses). Host output buffer. */
@@ -212,6 +243,30 @@ int b200v_batch_generate_dev(b200v_batch* h, void* d_syms, size_t sym_frame_stri
 int b200v_batch_depuncture_dev(b200v_batch* h, const void* d_punctured, size_t in_stride_bytes, size_t in_offset_syms,
                                const uint8_t* puncture_code, int code_len, void* d_syms, size_t out_stride_bytes,
                                size_t out_offset_syms, int n_out_syms, int unpunctured_value, int* consumed);
+
+/* Depuncturing FUSED into the decode: only the transmitted symbols exist in memory / cross PCIe.
+ * b200v_batch_set_puncturing installs the puncturing pattern of one update call -- normally a whole frame -- as the list
+ * of segments decode_punctured_symbols is called with (puncture_code_helpers.h:17-55; run_punctured_decoder.cpp:260-282:
+ * code, code length, full-rate symbols requested; the code index restarts at 0 in every segment). The segments must cover
+ * a multiple of R symbols. *n_transmitted (may be NULL) = transmitted symbols per frame. n_segments = 0 removes the pattern.
+ * b200v_batch_update_punctured_dev then consumes (sum of n_out_syms) / R trellis steps per frame from the TRANSMITTED
+ * symbols at d_punctured + f * frame_stride_bytes: the K=7 register kernels and the K=9 / K=15 group kernels gather
+ * through the pattern inside their symbol fetch (a symbol that was not transmitted becomes unpunctured_value in
+ * registers); the other kernel families expand into a staging buffer first. Results are bit-identical to
+ * b200v_batch_depuncture_dev + b200v_batch_update_dev.
+ * b200v_batch_decode_punctured[_dev]: init + update_punctured + chainback(nbits, 0), the pattern must cover frame_steps;
+ * the host entry copies n_transmitted symbols per frame, densely packed, in pipelined chunks of frames. */
+typedef struct b200v_puncture_segment {
+    const uint8_t* code;    /* code_len flags: non-zero = the symbol at this position was transmitted */
+    int code_len;
+    int n_out_syms;         /* full-rate symbols this segment produces */
+} b200v_puncture_segment;
+int b200v_batch_set_puncturing(b200v_batch* h, const b200v_puncture_segment* segments, int n_segments,
+                               int unpunctured_value, int* n_transmitted);
+int b200v_batch_update_punctured_dev(b200v_batch* h, const void* d_punctured, size_t frame_stride_bytes);
+int b200v_batch_decode_punctured_dev(b200v_batch* h, const void* d_punctured, size_t in_stride_bytes, uint8_t* d_data,
+                                     size_t out_stride_bytes, unsigned nbits);
+int b200v_batch_decode_punctured(b200v_batch* h, const void* punctured, uint8_t* data, unsigned nbits);
 
 /* ---- multi-GPU inside one process (frames are independent; no collective) ----
  * Shard g of G owns the contiguous frames [g*B/G, (g+1)*B/G). */

@@ -113,6 +113,10 @@ struct K7Args {
     int one, neg1;                 // 1 and -1, opaque to ptxas: multipliers that keep plain adds on the FMA pipe
     int zero;                      // 0, opaque to ptxas: third operand that keeps an add on the ALU pipe (IADD3)
     int two;                       // 2, opaque to ptxas: multiplier of the decision fold (keeps it an IMAD on the FMA pipe)
+    // depuncturing fused into the symbol fetch (PUNCT kernels): syms holds only the TRANSMITTED symbols of a frame;
+    // pidx[k] = index of full-rate symbol k (counted from this launch's first step) in that stream, or < 0: not
+    // transmitted, the decoder sees `fill` (puncture_code_helpers.h:17-55)
+    const int* pidx; int fill;
 };
 
 // ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
@@ -331,6 +335,21 @@ template <int R, int SB> struct PeriodBuf {
             }
         }
     }
+    // the same NSYM <= NB * R symbols gathered through the puncturing table (one index load, uniform over the warp, and
+    // one symbol load each)
+    __device__ __forceinline__ void load_punctured(const unsigned char* in, const int* idx, uint32_t fill, int nsym = NB * R) {
+#pragma unroll
+        for (int i = 0; i < WORDS; i++) w[i] = 0;
+#pragma unroll
+        for (int k = 0; k < NB * R; k++) {
+            if (k < nsym) {
+                const int ix = __ldg(idx + k);
+                uint32_t v = fill;
+                if (ix >= 0) v = SB == 2 ? (uint32_t)__ldg(reinterpret_cast<const unsigned short*>(in) + ix) : (uint32_t)__ldg(in + ix);
+                w[(k * SB) >> 2] |= v << (((k * SB) & 3) * 8);
+            }
+        }
+    }
     template <int POLICY>
     __device__ __forceinline__ void symbols(int step, int* sym) const {
 #pragma unroll
@@ -353,7 +372,7 @@ __device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE
 // (__launch_bounds__(128, 6) for the saturating policies -- 80 registers, 8-16 bytes of spills -- measured no faster:
 // spiral27 21.6 ms either way, spiral47 23.0 -> 23.7 ms. Round 2: the group kernels' decision collection for these
 // policies -- VIMNMX with predicate outputs + predicated FADDs -- takes 127 registers here (4 resident blocks): 23.9 ms.)
-template <int POLICY, class CODE>
+template <int POLICY, class CODE, bool PUNCT>
 __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     constexpr int R = CODE::R;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -400,10 +419,17 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     constexpr int SB = Arith<POLICY>::SB;
     using PBuf = PeriodBuf<R, SB>;
     PBuf cur, nxt;
-    if (periods > 0) cur.load(sp);
+    const uint32_t pfill = (uint32_t)a.fill & (SB == 2 ? 0xffffu : 0xffu);
+    if (periods > 0) {
+        if (PUNCT) cur.load_punctured(sp, a.pidx, pfill);
+        else cur.load(sp);
+    }
 #pragma unroll 1
     for (int pd = 0; pd < periods; pd++) {
-        if (pd + 1 < periods) nxt.load(sp + (size_t)(pd + 1) * NB * R * SB);
+        if (pd + 1 < periods) {
+            if (PUNCT) nxt.load_punctured(sp, a.pidx + (size_t)(pd + 1) * NB * R, pfill);
+            else nxt.load(sp + (size_t)(pd + 1) * NB * R * SB);
+        }
         unsigned long long d0, d1, d2, d3, d4, d5;
         run_step<POLICY, CODE, 0>(w, cur, a, off, &d0);
         run_step<POLICY, CODE, 1>(w, cur, a, off, &d1);
@@ -439,13 +465,16 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     if (rem > 0) {
         PBuf tb;
         const unsigned char* tp = sp + (size_t)periods * NB * R * SB;
+        if (PUNCT) tb.load_punctured(sp, a.pidx + (size_t)periods * NB * R, pfill, rem * R);
+        else {
 #pragma unroll
-        for (int i = 0; i < PBuf::WORDS; i++) {
-            uint32_t v = 0;
+            for (int i = 0; i < PBuf::WORDS; i++) {
+                uint32_t v = 0;
 #pragma unroll
-            for (int b = 0; b < 4; b++)
-                if (i * 4 + b < rem * R * SB) v |= (uint32_t)__ldg(tp + i * 4 + b) << (8 * b);
-            tb.w[i] = v;
+                for (int b = 0; b < 4; b++)
+                    if (i * 4 + b < rem * R * SB) v |= (uint32_t)__ldg(tp + i * 4 + b) << (8 * b);
+                tb.w[i] = v;
+            }
         }
         unsigned long long d;
         if (rem > 0) { run_step<POLICY, CODE, 0>(w, tb, a, off, &d); drow[0] = d; }
@@ -472,7 +501,8 @@ template <int POLICY, class CODE>
 static cudaError_t launch_one(const K7Args& a, cudaStream_t st) {
     const int threads = 128;
     const int blocks = (a.count + threads - 1) / threads;
-    acs_k7_kernel<POLICY, CODE><<<blocks, threads, 0, st>>>(a);
+    if (a.pidx) acs_k7_kernel<POLICY, CODE, true><<<blocks, threads, 0, st>>>(a);
+    else acs_k7_kernel<POLICY, CODE, false><<<blocks, threads, 0, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -525,9 +555,10 @@ bool k7_supported(const CodecParams& c) {
 
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st) {
+                          int frame0, int count, cudaStream_t st, const int* pidx, int fill) {
     if (count <= 0 || nsteps <= 0) return cudaSuccess;
     k7::K7Args a;
+    a.pidx = pidx; a.fill = fill;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;

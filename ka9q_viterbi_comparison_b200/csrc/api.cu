@@ -165,6 +165,9 @@ struct b200v_batch {
     K24GraphCache k24_graph;     // K=24: captured step loop of the last update call
     bool user_variant = false;   // set_variant() was called: no automatic family changes
     int tb_mode = 0, tb_warmup = 0;   // b200v_batch_set_traceback
+    // puncturing pattern of a frame (b200v_batch_set_puncturing): gather table over the full-rate symbols
+    int* d_pidx = nullptr; int punct_steps = 0, punct_tx = 0, punct_fill = 0;
+    void* d_punct_stage = nullptr; size_t punct_stage_bytes = 0;
     // lazily allocated staging for the host-pointer entry points
     void* d_syms_stage = nullptr; size_t syms_stage_bytes = 0;
     uint8_t* d_out_stage = nullptr; size_t out_stage_bytes = 0;
@@ -176,7 +179,7 @@ static void free_all(b200v_batch* h) {
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
     k24_graph_cache_release(&h->k24_graph);
     cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase); cudaFree(h->d_scan); cudaFree(h->d_best);
-    cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage);
+    cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage); cudaFree(h->d_pidx); cudaFree(h->d_punct_stage);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
     if (h->ev_c0) cudaEventDestroy(h->ev_c0);
@@ -352,10 +355,9 @@ static int wy16_symbol_limit(const CodecParams& c) {
 }
 
 // Returns 1 if every symbol of this update is inside the specialised kernels' range, 0 if not, < 0 on error.
-static int wy16_symbols_in_range(b200v_batch* h, const void* d_syms, size_t stride_bytes, int nsteps) {
+static int wy16_symbols_in_range(b200v_batch* h, const void* d_syms, size_t stride_bytes, int per_frame) {
     if (!h->d_scan) CUDA_TRY(cudaMalloc(&h->d_scan, sizeof(int)));
     CUDA_TRY(cudaMemsetAsync(h->d_scan, 0, sizeof(int), h->stream));
-    const int per_frame = nsteps * h->c.R;
     const size_t total = (size_t)per_frame * h->n_frames;
     int blocks = (int)((total + 1023) / 1024);
     if (blocks > 148 * 8) blocks = 148 * 8;
@@ -370,10 +372,26 @@ static int wy16_symbols_in_range(b200v_batch* h, const void* d_syms, size_t stri
 }
 
 // Launch the ACS kernel of the instance's family for frames [f0, f0 + cnt) on stream st.
+static int ensure_stage(void** p, size_t* have, size_t need);
+
+// pidx != nullptr: d_syms holds only the transmitted symbols (stride = bytes per frame of that stream) and pidx is the
+// gather table of this launch's steps. The K=7 register kernels and the group kernels fetch through the table; the other
+// families get the frames expanded into the full-rate staging buffer first.
 static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride, int nsteps, int step0, int f0, int cnt,
-                               cudaStream_t st) {
+                               cudaStream_t st, const int* pidx = nullptr) {
     const CodecParams& c = h->c;
     if (nsteps <= 0 || cnt <= 0) return B200V_OK;
+    const bool fused = h->variant == 2 && (h->layout == DL_GRP_INTERLEAVED || h->layout == DL_K7_INTERLEAVED);
+    if (pidx && !fused) {
+        const size_t srow = (size_t)nsteps * c.R * c.sym_bytes;
+        if (h->syms_stage_bytes < srow * h->n_frames)
+            return fail(B200V_ERR_STATE, "full-rate staging buffer missing for the depuncturing expansion");
+        CUDA_TRY(launch_depuncture_gather(d_syms, stride, h->d_syms_stage, srow, pidx, nsteps * c.R, h->punct_fill,
+                                          c.sym_bytes, f0, cnt, st));
+        h->launches++;
+        d_syms = h->d_syms_stage; stride = srow; pidx = nullptr;
+    }
+    const int pfill = h->punct_fill;
     if (h->layout == DL_CANONICAL) {
         if (f0 != 0 || cnt != h->n_frames) return fail(B200V_ERR_STATE, "the K=24 family works on whole batches");
         CUDA_TRY(launch_acs_k24(c, d_syms, stride, nsteps, step0, (uint32_t*)h->d_dec, h->dec_rows,
@@ -381,7 +399,7 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
                                 &h->launches, &h->k24_graph, st));
     } else if (h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
         CUDA_TRY(launch_acs_grp(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
-                                h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
+                                h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, pidx, pfill));
         h->launches++;
     } else if (h->variant == 2 && h->layout == DL_SMALLK_INTERLEAVED) {
         GenericArgs a{};
@@ -392,7 +410,7 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
         h->launches++;
     } else if (h->variant == 2) {
         CUDA_TRY(launch_acs_k7(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
-                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st));
+                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, pidx, pfill));
         h->launches++;
     } else {
         GenericArgs a{};
@@ -422,7 +440,7 @@ extern "C" int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t
     CUDA_TRY(cudaSetDevice(h->device));
     if (c.policy == P_WY_U16 && h->variant == 2 && h->layout != DL_SMALLK_INTERLEAVED && h->layout != DL_CANONICAL &&
         nsteps > 0) {   // the small-K and K=24 kernels compute in int32: exact for any input
-        const int ok = wy16_symbols_in_range(h, d_syms, frame_stride_bytes, nsteps);
+        const int ok = wy16_symbols_in_range(h, d_syms, frame_stride_bytes, nsteps * c.R);
         if (ok < 0) return ok;
         if (!ok) {
             if (h->cursor != 0)
@@ -554,17 +572,29 @@ extern "C" int b200v_batch_chainback_results(b200v_batch* h, int* results) {
 // Batch entry point. Large batches are cut into chunks of frames that flow through NPIPE streams, each chunk
 // doing H2D copy -> update -> chainback -> D2H copy on its stream, so that the copies of one chunk overlap the
 // kernels of another (the path is PCIe-bound end to end: R*T symbol bytes in per decoded bit).
-extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits) {
+static int decode_host(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits, bool punct) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     if (!syms || (!data && nbits)) return fail(B200V_ERR_ARG, "NULL buffer");
     const CodecParams& c = h->c;
-    const size_t srow = (size_t)h->frame_steps * c.R * c.sym_bytes;
+    if (punct && (!h->d_pidx || h->punct_steps != h->frame_steps))
+        return fail(B200V_ERR_STATE, "b200v_batch_decode_punctured needs a puncturing pattern that covers the %d steps of a frame "
+                    "(b200v_batch_set_puncturing; the installed one covers %d)", h->frame_steps, h->punct_steps);
+    const size_t srow = (size_t)h->frame_steps * c.R * c.sym_bytes;      // full-rate bytes per frame
+    const size_t irow = punct ? (size_t)h->punct_tx * c.sym_bytes : srow; // bytes per frame that cross PCIe
     const size_t orow = (nbits + 7) / 8;
     const int min_chunk = 2048;
     if (h->layout == DL_CANONICAL || c.policy == P_WY_U16 || h->n_frames < 2 * min_chunk || orow == 0) {
         int rc = b200v_batch_init(h, 0);
         if (rc) return rc;
-        rc = b200v_batch_update(h, syms, srow, h->frame_steps);
+        if (punct) {
+            CUDA_TRY(cudaSetDevice(h->device));
+            rc = ensure_stage(&h->d_punct_stage, &h->punct_stage_bytes, irow * h->n_frames);
+            if (rc) return rc;
+            CUDA_TRY(cudaMemcpyAsync(h->d_punct_stage, syms, irow * h->n_frames, cudaMemcpyHostToDevice, h->stream));
+            rc = b200v_batch_update_punctured_dev(h, h->d_punct_stage, irow);
+        } else {
+            rc = b200v_batch_update(h, syms, srow, h->frame_steps);
+        }
         if (rc) return rc;
         return b200v_batch_chainback(h, data, orow, nbits, 0);
     }
@@ -573,8 +603,13 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
         return fail(B200V_ERR_STATE, "chainback of %u bits needs %u decision rows, %d allocated", nbits,
                     rows_needed, h->dec_rows);
     CUDA_TRY(cudaSetDevice(h->device));
-    int rc = ensure_stage(&h->d_syms_stage, &h->syms_stage_bytes, srow * h->n_frames);
+    const bool fused = h->variant == 2 && (h->layout == DL_GRP_INTERLEAVED || h->layout == DL_K7_INTERLEAVED);
+    int rc = B200V_OK;
+    if (!punct || !fused) rc = ensure_stage(&h->d_syms_stage, &h->syms_stage_bytes, srow * h->n_frames);
     if (rc) return rc;
+    if (punct) rc = ensure_stage(&h->d_punct_stage, &h->punct_stage_bytes, irow * h->n_frames);
+    if (rc) return rc;
+    char* d_in = (char*)(punct ? h->d_punct_stage : h->d_syms_stage);
     rc = ensure_stage((void**)&h->d_out_stage, &h->out_stage_bytes, orow * h->n_frames);
     if (rc) return rc;
     for (int i = 0; i < b200v_batch::NPIPE; i++)
@@ -595,10 +630,10 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
     for (int f0 = 0; f0 < h->n_frames && rc == B200V_OK && ce == cudaSuccess; f0 += chunk, k++) {
         const int cnt = (h->n_frames - f0 < chunk) ? h->n_frames - f0 : chunk;
         cudaStream_t st = h->pipe[k % b200v_batch::NPIPE];
-        ce = cudaMemcpyAsync((char*)h->d_syms_stage + (size_t)f0 * srow, (const char*)syms + (size_t)f0 * srow,
-                             (size_t)cnt * srow, cudaMemcpyHostToDevice, st);
+        ce = cudaMemcpyAsync(d_in + (size_t)f0 * irow, (const char*)syms + (size_t)f0 * irow,
+                             (size_t)cnt * irow, cudaMemcpyHostToDevice, st);
         if (ce != cudaSuccess) break;
-        rc = launch_update_range(h, h->d_syms_stage, srow, nsteps, 0, f0, cnt, st);
+        rc = launch_update_range(h, d_in, irow, nsteps, 0, f0, cnt, st, punct ? h->d_pidx : nullptr);
         if (rc) break;
         rc = launch_chainback_range(h, h->d_out_stage, orow, nbits, 0, f0, cnt, st, nullptr, true);
         if (rc) break;
@@ -617,6 +652,13 @@ extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* dat
                     cudaGetErrorString(ce));
     h->cursor = nsteps;
     return B200V_OK;
+}
+
+extern "C" int b200v_batch_decode(b200v_batch* h, const void* syms, uint8_t* data, unsigned nbits) {
+    return decode_host(h, syms, data, nbits, false);
+}
+extern "C" int b200v_batch_decode_punctured(b200v_batch* h, const void* punctured, uint8_t* data, unsigned nbits) {
+    return decode_host(h, punctured, data, nbits, true);
 }
 
 // Device-pointer batch entry: init + update(frame_steps) + chainback(nbits) with symbols and output already in
@@ -644,6 +686,120 @@ extern "C" int b200v_batch_sync(b200v_batch* h) {
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     return B200V_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// sliding-window decode of continuous streams
+// ---------------------------------------------------------------------------------------------------
+// A b200v_batch whose decision rows are used as a ring: logical row r (trellis step since reset) lives at row r % W,
+// W = depth + chunk. depth is a multiple of chunk, so an update launch of `chunk` steps never wraps, and every ring
+// position is always written by the same step-in-launch (the row phases of the register kernels stay valid).
+struct b200v_stream {
+    b200v_batch* b = nullptr;
+    int depth = 0, chunk = 0, W = 0;
+    long long steps = 0, emitted = 0;
+};
+
+extern "C" b200v_stream* b200v_stream_create(int codec, int K, int R, const int* poly, int n_streams, int depth, int chunk,
+                                             int device, const b200v_wy_config* wy_config) {
+    CodecParams c;
+    if (fill_params(c, codec, K, R, poly, wy_config) != B200V_OK) return nullptr;
+    if (c.K > 16) { fail(B200V_ERR_ARG, "stream decoding exists for K <= 16 (K=%d)", c.K); return nullptr; }
+    if (chunk <= 0 || chunk % 8 || depth <= 0 || depth % chunk || depth < c.K - 1) {
+        fail(B200V_ERR_ARG, "stream geometry: chunk=%d must be a positive multiple of 8, depth=%d a multiple of chunk and "
+             ">= K-1 = %d", chunk, depth, c.K - 1);
+        return nullptr;
+    }
+    b200v_stream* s = new (std::nothrow) b200v_stream();
+    if (!s) { fail(B200V_ERR_NOMEM, "host allocation failed"); return nullptr; }
+    s->depth = depth; s->chunk = chunk; s->W = depth + chunk;
+    // b200v_batch_create allocates frame_steps + K-1 rows
+    s->b = b200v_batch_create(codec, K, R, poly, s->W - (c.K - 1), n_streams, device, wy_config);
+    if (!s->b) { delete s; return nullptr; }
+    if (s->b->c.policy == P_WY_U16) {      // exact for any int16 input: no per-update range scan, no family change mid-stream
+        s->b->variant = exact_variant(s->b); s->b->layout = DL_BALLOT_FRAME_MAJOR; s->b->user_variant = true;
+    }
+    return s;
+}
+
+extern "C" void b200v_stream_destroy(b200v_stream* s) {
+    if (!s) return;
+    b200v_batch_destroy(s->b);
+    delete s;
+}
+
+extern "C" int b200v_stream_reset(b200v_stream* s, int starting_state) {
+    if (!s) return fail(B200V_ERR_ARG, "NULL stream");
+    s->steps = 0; s->emitted = 0;
+    return b200v_batch_init(s->b, starting_state);
+}
+
+static int stream_traceback(b200v_stream* s, int endstate, unsigned long long first_bit, unsigned nbits, int state_bits,
+                            uint8_t* d_out, size_t out_stride) {
+    b200v_batch* h = s->b;
+    if (nbits == 0) return B200V_OK;
+    if (!d_out) return fail(B200V_ERR_ARG, "NULL output buffer");
+    if (out_stride < (nbits + 7) / 8 && h->n_frames > 1) return fail(B200V_ERR_ARG, "output stride %zu smaller than %u bits", out_stride, nbits);
+    StreamTracebackArgs t{};
+    ChainbackArgs& a = t.a;
+    a.c = h->c; a.layout = h->layout; a.dec = h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
+    a.row_phase = h->d_row_phase; a.n_frames = h->n_frames; a.frame0 = 0; a.count = h->n_frames;
+    a.metrics = h->d_metrics; a.out = d_out; a.out_stride = out_stride; a.nbits = nbits;
+    a.endstate = endstate < 0 ? 0u : (unsigned)endstate; a.endstates = nullptr; a.results = nullptr;
+    if (endstate < 0) {
+        if (!h->d_best) CUDA_TRY(cudaMalloc(&h->d_best, (size_t)h->n_frames * sizeof(unsigned)));
+        CUDA_TRY(launch_best_state(h->c, h->d_metrics, h->d_best, h->n_frames, h->stream));
+        h->launches++;
+        a.endstates = h->d_best;
+    }
+    t.ring_rows = (unsigned)s->W; t.top_row = (unsigned long long)(s->steps - 1); t.first_bit = first_bit; t.state_bits = state_bits;
+    CUDA_TRY(launch_stream_traceback(t, h->stream));
+    h->launches++;
+    return B200V_OK;
+}
+
+extern "C" int b200v_stream_push_dev(b200v_stream* s, const void* d_syms, size_t sym_stride_bytes, uint8_t* d_out,
+                                     size_t out_stride_bytes, unsigned* bits_out) {
+    if (!s) return fail(B200V_ERR_ARG, "NULL stream");
+    if (!d_syms) return fail(B200V_ERR_ARG, "NULL symbol buffer");
+    b200v_batch* h = s->b;
+    if (bits_out) *bits_out = 0;
+    if (h->n_frames > 1 && sym_stride_bytes < (size_t)s->chunk * h->c.R * h->c.sym_bytes)
+        return fail(B200V_ERR_ARG, "stream stride %zu smaller than one chunk's symbols", sym_stride_bytes);
+    CUDA_TRY(cudaSetDevice(h->device));
+    const int pos = (int)(s->steps % s->W);
+    int rc = launch_update_range(h, d_syms, sym_stride_bytes, s->chunk, pos, 0, h->n_frames, h->stream);
+    if (rc) return rc;
+    s->steps += s->chunk;
+    h->cursor = pos + s->chunk;
+    if (s->steps < s->W) return B200V_OK;
+    const unsigned long long first = (unsigned long long)(s->steps - s->W);
+    rc = stream_traceback(s, -1, first, (unsigned)s->chunk, 0, d_out, out_stride_bytes);
+    if (rc) return rc;
+    s->emitted = s->steps - s->depth;
+    if (bits_out) *bits_out = (unsigned)s->chunk;
+    return B200V_OK;
+}
+
+extern "C" int b200v_stream_flush_dev(b200v_stream* s, int endstate, uint8_t* d_out, size_t out_stride_bytes, unsigned* bits_out) {
+    if (!s) return fail(B200V_ERR_ARG, "NULL stream");
+    b200v_batch* h = s->b;
+    if (bits_out) *bits_out = 0;
+    if (endstate >= h->c.S) return fail(B200V_ERR_ARG, "end state %d out of range", endstate);
+    const long long end = endstate < 0 ? s->steps : s->steps - (h->c.K - 1);
+    if (end <= s->emitted) return B200V_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const unsigned nbits = (unsigned)(end - s->emitted);
+    int rc = stream_traceback(s, endstate, (unsigned long long)s->emitted, nbits, endstate < 0 ? 1 : 0, d_out, out_stride_bytes);
+    if (rc) return rc;
+    s->emitted = end;
+    if (bits_out) *bits_out = nbits;
+    return B200V_OK;
+}
+
+extern "C" long long b200v_stream_steps(const b200v_stream* s) { return s ? s->steps : 0; }
+extern "C" long long b200v_stream_emitted(const b200v_stream* s) { return s ? s->emitted : 0; }
+extern "C" int b200v_stream_sync(b200v_stream* s) { return s ? b200v_batch_sync(s->b) : fail(B200V_ERR_ARG, "NULL stream"); }
+extern "C" b200v_batch* b200v_stream_batch(b200v_stream* s) { return s ? s->b : nullptr; }
 
 // ---------------------------------------------------------------------------------------------------
 // introspection
@@ -808,6 +964,92 @@ extern "C" int b200v_batch_depuncture_dev(b200v_batch* h, const void* d_puncture
     CUDA_TRY(launch_depuncture(a, h->c.sym_bytes, h->n_frames, h->stream));
     h->launches++;
     return B200V_OK;
+}
+
+// The puncturing pattern of a whole frame as a gather table: entry k = position of full-rate symbol k in the frame's
+// transmitted stream, or -1. Segment by segment exactly as decode_punctured_symbols walks them
+// (puncture_code_helpers.h:17-55: the code index restarts at 0 in every segment; run_punctured_decoder.cpp:260-282).
+extern "C" int b200v_batch_set_puncturing(b200v_batch* h, const b200v_puncture_segment* segments, int n_segments,
+                                          int unpunctured_value, int* n_transmitted) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (n_transmitted) *n_transmitted = 0;
+    CUDA_TRY(cudaSetDevice(h->device));
+    if (n_segments <= 0) {
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_pidx); h->d_pidx = nullptr; h->punct_steps = h->punct_tx = 0;
+        return B200V_OK;
+    }
+    if (!segments) return fail(B200V_ERR_ARG, "NULL segment list");
+    std::vector<int> idx;
+    int tx = 0;
+    for (int g = 0; g < n_segments; g++) {
+        const b200v_puncture_segment& sg = segments[g];
+        if (!sg.code || sg.code_len <= 0 || sg.n_out_syms < 0)
+            return fail(B200V_ERR_ARG, "puncture segment %d: code=%p code_len=%d n_out_syms=%d", g, (const void*)sg.code,
+                        sg.code_len, sg.n_out_syms);
+        for (int k = 0; k < sg.n_out_syms; k++) idx.push_back(sg.code[k % sg.code_len] ? tx++ : -1);
+    }
+    if (idx.empty() || idx.size() % (size_t)h->c.R)
+        return fail(B200V_ERR_ARG, "the segments cover %zu full-rate symbols: not a positive multiple of R = %d", idx.size(), h->c.R);
+    const int steps = (int)(idx.size() / (size_t)h->c.R);
+    if (steps > h->dec_rows) return fail(B200V_ERR_ARG, "the segments cover %d steps, the instance holds %d", steps, h->dec_rows);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    cudaFree(h->d_pidx); h->d_pidx = nullptr;
+    CUDA_TRY(cudaMalloc(&h->d_pidx, idx.size() * sizeof(int)));
+    CUDA_TRY(cudaMemcpy(h->d_pidx, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+    h->punct_steps = steps; h->punct_tx = tx; h->punct_fill = unpunctured_value;
+    if (n_transmitted) *n_transmitted = tx;
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_update_punctured_dev(b200v_batch* h, const void* d_punctured, size_t frame_stride_bytes) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (!h->d_pidx) return fail(B200V_ERR_STATE, "no puncturing pattern installed (b200v_batch_set_puncturing)");
+    if (!d_punctured) return fail(B200V_ERR_ARG, "NULL symbol buffer");
+    const CodecParams& c = h->c;
+    int nsteps = h->punct_steps;
+    if (policy_is_spiral(c.policy)) { h->cursor = 0; nsteps = (nsteps / 2) * 2; }     // spiral27.cpp:383-386
+    if (h->cursor + nsteps > h->dec_rows)
+        return fail(B200V_ERR_STATE, "update of %d steps at step %d exceeds the %d decision rows allocated", nsteps,
+                    h->cursor, h->dec_rows);
+    if (h->n_frames > 1 && frame_stride_bytes < (size_t)h->punct_tx * c.sym_bytes)
+        return fail(B200V_ERR_ARG, "frame stride %zu smaller than one frame's %d transmitted symbols", frame_stride_bytes, h->punct_tx);
+    CUDA_TRY(cudaSetDevice(h->device));
+    if (c.policy == P_WY_U16 && h->variant == 2 && h->layout != DL_SMALLK_INTERLEAVED && h->layout != DL_CANONICAL) {
+        int ok = wy16_symbols_in_range(h, d_punctured, frame_stride_bytes, h->punct_tx);
+        if (ok < 0) return ok;
+        const int f = h->punct_fill < 0 ? -h->punct_fill : h->punct_fill;
+        if (f > wy16_symbol_limit(c)) ok = 0;
+        if (!ok) {
+            if (h->cursor != 0)
+                return fail(B200V_ERR_ARG, "int16 symbols beyond +-%d in a continued update: select the generic family "
+                            "(variant 1) after init", wy16_symbol_limit(c));
+            h->variant = exact_variant(h); h->layout = DL_BALLOT_FRAME_MAJOR;
+        }
+    }
+    const bool fused = h->variant == 2 && (h->layout == DL_GRP_INTERLEAVED || h->layout == DL_K7_INTERLEAVED);
+    if (!fused) {
+        int rc = ensure_stage(&h->d_syms_stage, &h->syms_stage_bytes, (size_t)nsteps * c.R * c.sym_bytes * h->n_frames);
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaEventRecord(h->ev_u0, h->stream));
+    int rc = launch_update_range(h, d_punctured, frame_stride_bytes, nsteps, h->cursor, 0, h->n_frames, h->stream, h->d_pidx);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev_u1, h->stream));
+    h->timed_update = true;
+    h->cursor += nsteps;
+    return B200V_OK;
+}
+
+extern "C" int b200v_batch_decode_punctured_dev(b200v_batch* h, const void* d_punctured, size_t in_stride_bytes,
+                                                uint8_t* d_data, size_t out_stride_bytes, unsigned nbits) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (!d_punctured || (!d_data && nbits)) return fail(B200V_ERR_ARG, "NULL buffer");
+    int rc = b200v_batch_init(h, 0);
+    if (rc) return rc;
+    rc = b200v_batch_update_punctured_dev(h, d_punctured, in_stride_bytes);
+    if (rc) return rc;
+    return b200v_batch_chainback_dev(h, d_data, out_stride_bytes, nbits, 0);
 }
 
 // ---------------------------------------------------------------------------------------------------

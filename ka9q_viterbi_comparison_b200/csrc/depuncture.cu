@@ -25,7 +25,32 @@ __global__ void depuncture_kernel(const DepunctureArgs a) {
     }
 }
 
+// the same expansion through a precomputed gather table (b200v_batch_set_puncturing): out[k] = in[idx[k]] or fill.
+// Used by the kernel families whose symbol fetch does not take the table itself.
+template <typename T>
+__global__ void gather_kernel(const unsigned char* in, size_t in_stride, unsigned char* out, size_t out_stride,
+                              const int* idx, int n_out, int fill, int frame0) {
+    const int frame = frame0 + blockIdx.x;
+    const T* pi = reinterpret_cast<const T*>(in + (size_t)frame * in_stride);
+    T* po = reinterpret_cast<T*>(out + (size_t)frame * out_stride);
+    for (int k = blockIdx.y * blockDim.x + threadIdx.x; k < n_out; k += gridDim.y * blockDim.x) {
+        const int ix = __ldg(idx + k);
+        po[k] = ix >= 0 ? pi[ix] : (T)fill;
+    }
+}
+
 }  // namespace
+
+cudaError_t launch_depuncture_gather(const void* in, size_t in_stride, void* out, size_t out_stride, const int* idx,
+                                     int n_out, int fill, int sym_bytes, int frame0, int count, cudaStream_t st) {
+    if (count <= 0 || n_out <= 0) return cudaSuccess;
+    int bx = (n_out + 255) / 256;
+    if (bx > 64) bx = 64;
+    const dim3 grid((unsigned)count, (unsigned)bx);
+    if (sym_bytes == 2) gather_kernel<int16_t><<<grid, 256, 0, st>>>((const unsigned char*)in, in_stride, (unsigned char*)out, out_stride, idx, n_out, fill, frame0);
+    else gather_kernel<uint8_t><<<grid, 256, 0, st>>>((const unsigned char*)in, in_stride, (unsigned char*)out, out_stride, idx, n_out, fill, frame0);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_depuncture(const DepunctureArgs& a, int sym_bytes, int n_frames, cudaStream_t st) {
     if (n_frames <= 0 || a.n_out <= 0) return cudaSuccess;

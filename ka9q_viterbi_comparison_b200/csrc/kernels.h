@@ -41,14 +41,17 @@ cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecPara
 bool k7_supported(const CodecParams& c);
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st);
+                          int frame0, int count, cudaStream_t st, const int* pidx = nullptr, int fill = 0);
+// pidx != nullptr: depuncturing fused into the symbol fetch -- `syms` holds only each frame's transmitted symbols and
+// pidx[k] is the position of full-rate symbol k of this launch in that stream, or < 0 for a symbol that was not transmitted
+// (the decoder then sees `fill`). The K=7 register kernels and the group kernels take it.
 
 // ---- group kernels for K=9 / K=15 (acs_grp.cu): decisions as one u64 per (row, frame, thread of the frame) ----
 bool grp_supported(const CodecParams& c);
 int grp_threads_per_frame(const CodecParams& c);
 cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                           int frame0, int count, cudaStream_t st);
+                           int frame0, int count, cudaStream_t st, const int* pidx = nullptr, int fill = 0);
 
 // ---- K=24 (acs_k24.cu): one launch per trellis step, ping-pong metric buffers, canonical decision rows ----
 // replay cache of the captured step loop of one update call (acs_k24.cu)
@@ -114,6 +117,9 @@ struct DepunctureArgs {
     uint16_t prefix[MAX_PUNCTURE_LEN + 1];                  // prefix[j] = kept positions among code[0..j)
 };
 cudaError_t launch_depuncture(const DepunctureArgs& a, int sym_bytes, int n_frames, cudaStream_t st);
+// expansion of frames [frame0, frame0 + count) through a gather table: out[f][k] = idx[k] >= 0 ? in[f][idx[k]] : fill
+cudaError_t launch_depuncture_gather(const void* in, size_t in_stride, void* out, size_t out_stride, const int* idx,
+                                     int n_out, int fill, int sym_bytes, int frame0, int count, cudaStream_t st);
 
 // ---- synthetic input generator (generate.cu) ------------------------------------------------------
 struct GenerateArgs {

@@ -45,6 +45,11 @@ class WyConfig(C.Structure):
                 ("initial_non_start_error", C.c_uint), ("renormalisation_threshold", C.c_uint)]
 
 
+class PunctureSegment(C.Structure):
+    """b200v_puncture_segment: one call of the reference's decode_punctured_symbols (code, length, symbols requested)."""
+    _fields_ = [("code", C.POINTER(C.c_uint8)), ("code_len", C.c_int), ("n_out_syms", C.c_int)]
+
+
 _lib = None
 
 
@@ -89,6 +94,15 @@ def load_library():
         "b200v_decode_noalloc_dev": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(WyConfig), i32, i32, vp, sz, vp, sz, u32,
                                            i32, vp]),
         "b200v_batch_sync": (i32, [vp]),
+        "b200v_stream_create": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, i32, i32, C.POINTER(WyConfig)]),
+        "b200v_stream_destroy": (None, [vp]),
+        "b200v_stream_reset": (i32, [vp, i32]),
+        "b200v_stream_push_dev": (i32, [vp, vp, sz, vp, sz, C.POINTER(u32)]),
+        "b200v_stream_flush_dev": (i32, [vp, i32, vp, sz, C.POINTER(u32)]),
+        "b200v_stream_steps": (C.c_longlong, [vp]),
+        "b200v_stream_emitted": (C.c_longlong, [vp]),
+        "b200v_stream_sync": (i32, [vp]),
+        "b200v_stream_batch": (vp, [vp]),
         "b200v_batch_get_decisions": (i32, [vp, i32, i32, i32, vp]),
         "b200v_batch_get_metrics": (i32, [vp, i32, vp]),
         "b200v_batch_steps_done": (i32, [vp]),
@@ -96,6 +110,10 @@ def load_library():
         "b200v_batch_launch_count": (C.c_longlong, [vp]),
         "b200v_batch_generate_dev": (i32, [vp, vp, sz, vp, sz, u32, u64, u64, i32, i32, i32, i32, i32]),
         "b200v_batch_depuncture_dev": (i32, [vp, vp, sz, sz, vp, i32, vp, sz, sz, i32, i32, C.POINTER(i32)]),
+        "b200v_batch_set_puncturing": (i32, [vp, C.POINTER(PunctureSegment), i32, i32, C.POINTER(i32)]),
+        "b200v_batch_update_punctured_dev": (i32, [vp, vp, sz]),
+        "b200v_batch_decode_punctured_dev": (i32, [vp, vp, sz, vp, sz, u32]),
+        "b200v_batch_decode_punctured": (i32, [vp, vp, vp, u32]),
         "b200v_shard_range": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
         "b200v_sharded_create": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(WyConfig)]),
         "b200v_sharded_destroy": (None, [vp]),
@@ -125,9 +143,12 @@ EXPORTED_SYMBOLS = [
     "b200v_codec_symbol_bytes", "b200v_codec_metric_bytes", "b200v_batch_create", "b200v_batch_destroy",
     "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_set_traceback", "b200v_batch_init",
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
-    "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_decode_noalloc_dev", "b200v_batch_sync", "b200v_batch_get_decisions",
+    "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_decode_noalloc_dev", "b200v_batch_sync",
+    "b200v_stream_create", "b200v_stream_destroy", "b200v_stream_reset", "b200v_stream_push_dev", "b200v_stream_flush_dev",
+    "b200v_stream_steps", "b200v_stream_emitted", "b200v_stream_sync", "b200v_stream_batch", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
-    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_shard_range", "b200v_sharded_create",
+    "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_batch_set_puncturing", "b200v_batch_update_punctured_dev",
+    "b200v_batch_decode_punctured_dev", "b200v_batch_decode_punctured", "b200v_shard_range", "b200v_sharded_create",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
     "b200v_sharded_last_error", "b200v_bind_host_to_device", "b200v_device_alloc", "b200v_device_free",
     "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_host_is_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
@@ -238,6 +259,35 @@ class BatchDecoder:
                                                    C.byref(used)))
         return used.value
 
+    def set_puncturing(self, segments, fill=0):
+        """segments: [(code, n_out_syms), ...] as the reference passes them to decode_punctured_symbols, one per segment
+        of a frame; None / [] removes the pattern. Returns the transmitted symbols per frame."""
+        segments = list(segments or [])
+        keep = [np.ascontiguousarray(code, dtype=np.uint8) for code, _ in segments]
+        arr = (PunctureSegment * max(len(segments), 1))()
+        for i, (code, n_out) in enumerate(segments):
+            arr[i].code = keep[i].ctypes.data_as(C.POINTER(C.c_uint8))
+            arr[i].code_len = len(keep[i])
+            arr[i].n_out_syms = int(n_out)
+        n_tx = C.c_int(0)
+        _check(self.lib.b200v_batch_set_puncturing(self.h, arr, len(segments), fill, C.byref(n_tx)))
+        self.n_transmitted = n_tx.value
+        return n_tx.value
+
+    def update_punctured_dev(self, d_punctured, frame_stride_bytes):
+        _check(self.lib.b200v_batch_update_punctured_dev(self.h, _ptr(d_punctured), frame_stride_bytes))
+
+    def decode_punctured_dev(self, d_punctured, in_stride, d_out, out_stride, nbits):
+        _check(self.lib.b200v_batch_decode_punctured_dev(self.h, _ptr(d_punctured), in_stride, _ptr(d_out), out_stride, nbits))
+
+    def decode_punctured(self, punctured, total_bits):
+        """Host buffers: punctured [n_frames, n_transmitted] symbols -> decoded bytes; only those symbols cross PCIe."""
+        punctured = np.ascontiguousarray(punctured, dtype=self.sym_dtype).reshape(self.n_frames, -1)
+        assert punctured.shape[1] == self.n_transmitted
+        out = np.zeros((self.n_frames, (total_bits + 7) // 8), dtype=np.uint8)
+        _check(self.lib.b200v_batch_decode_punctured(self.h, punctured.ctypes.data, out.ctypes.data, total_bits))
+        return out
+
     def generate_dev(self, d_syms, sym_stride, d_data, data_stride, nbits, seed, frame0, amp_q8, sigma_q8,
                      mean_q8, lo, hi):
         _check(self.lib.b200v_batch_generate_dev(self.h, _ptr(d_syms), sym_stride, _ptr(d_data), data_stride,
@@ -299,6 +349,69 @@ class BatchDecoder:
             self.close()
         except Exception:
             pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+class StreamDecoder:
+    """Sliding-window decoder of ``n_streams`` continuous streams (b200v_stream_*): every ``push_dev`` consumes ``chunk``
+    trellis steps per stream and, once ``depth + chunk`` steps are in the ring, emits the ``chunk`` oldest bits traced
+    back from every stream's best state. ``flush_dev`` emits what is left at the end of the stream."""
+
+    def __init__(self, codec, n_streams, depth, chunk, K=0, R=0, poly=None, device=0, wy_config=None):
+        self.lib = load_library()
+        if isinstance(codec, str):
+            codec = CODEC_BY_NAME[codec]
+        k, r = C.c_int(0), C.c_int(0)
+        _check(self.lib.b200v_codec_shape(codec, C.byref(k), C.byref(r)))
+        self.K, self.R = k.value or K, r.value or R
+        poly = list(poly if poly is not None else STANDARD_POLYS[(self.K, self.R)])
+        self.codec, self.n_streams, self.depth, self.chunk = codec, n_streams, depth, chunk
+        self.sym_dtype = symbol_dtype(codec)
+        cfg = C.byref(wy_config) if wy_config is not None else None
+        self.h = self.lib.b200v_stream_create(codec, self.K, self.R, (C.c_int * len(poly))(*poly), n_streams, depth, chunk,
+                                              device, cfg)
+        if not self.h:
+            raise B200ViterbiError("b200v_stream_create failed: " + self.lib.b200v_last_error().decode())
+
+    def reset(self, starting_state=0):
+        _check(self.lib.b200v_stream_reset(self.h, starting_state))
+
+    def push_dev(self, d_syms, sym_stride, d_out, out_stride):
+        """Returns the number of bits emitted per stream by this push (0 or ``chunk``)."""
+        n = C.c_uint(0)
+        _check(self.lib.b200v_stream_push_dev(self.h, _ptr(d_syms), sym_stride, _ptr(d_out), out_stride, C.byref(n)))
+        return n.value
+
+    def flush_dev(self, d_out, out_stride, endstate=-1):
+        n = C.c_uint(0)
+        _check(self.lib.b200v_stream_flush_dev(self.h, endstate, _ptr(d_out), out_stride, C.byref(n)))
+        return n.value
+
+    @property
+    def steps(self):
+        return self.lib.b200v_stream_steps(self.h)
+
+    @property
+    def emitted(self):
+        return self.lib.b200v_stream_emitted(self.h)
+
+    def sync(self):
+        _check(self.lib.b200v_stream_sync(self.h))
+
+    def metrics(self, stream):
+        out = np.zeros(1 << (self.K - 1), dtype=metric_dtype(self.codec))
+        _check(self.lib.b200v_batch_get_metrics(self.lib.b200v_stream_batch(self.h), stream, out.ctypes.data))
+        return out
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200v_stream_destroy(self.h)
+            self.h = None
 
     def __enter__(self):
         return self

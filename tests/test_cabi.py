@@ -86,6 +86,6 @@ def test_k7_register_kernels_do_not_spill():
         pytest.skip("cuobjdump not available")
     assert os.path.exists(obj), "acs_k7.cu.o missing: the library was not built by ka9q_viterbi_comparison_b200.build"
     out = subprocess.run([tool, "-res-usage", obj], capture_output=True, text=True).stdout
-    m = re.search(r"acs_k7_kernelILi0ENS0_4CodeILi2ELi109ELi79ELi0ELi0EEEEE\S*:\s*\n\s*REG:(\d+) STACK:(\d+)", out)
+    m = re.search(r"acs_k7_kernelILi0ENS0_4CodeILi2ELi109ELi79ELi0ELi0EEELb0EEE\S*:\s*\n\s*REG:(\d+) STACK:(\d+)", out)
     assert m, "ka9q27 kernel not found in acs_k7.cu.o"
     assert int(m.group(1)) <= 80, m.groups()

@@ -135,3 +135,123 @@ def test_gpu_depuncture_more_than_65535_frames():
     for f in (0, 65535, 65536, n_frames - 1):
         want, _ = po.depuncture(tx[f], code, n_out, 0, R)
         assert np.array_equal(got[f], want), f
+
+
+def _punctured_batch(c, R, K, nbytes, n_frames, segs, sigma, seed):
+    """Full-rate frames from the generator, punctured on the host segment by segment. Returns (data, full, tx)."""
+    datas, fulls, txs = [], [], []
+    for f in range(n_frames):
+        d, full = o.make_frame(c, nbytes, sigma if f else 0.0, seed=seed, frame=f)
+        pos, parts = 0, []
+        for code, n_out in segs:
+            parts.append(po.puncture(full[pos:pos + n_out], code))
+            pos += n_out
+        assert pos == full.size
+        datas.append(d); fulls.append(full); txs.append(np.concatenate(parts))
+    return np.stack(datas), np.stack(fulls), np.stack(txs).astype(o.sym_dtype(c))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,variant", [("wy_sse_u8_k7r4", 2), ("wy_sse_u8_k7r4", 3), ("wy_sse_u16_k7r4", 2), ("spiral47", 2),
+                                          ("ka9q27", 2), ("ka9q27", 1), ("ka9q29", 2), ("spiral49", 2), ("wy_sse_u8_k9r2", 2),
+                                          ("ka9q615", 2), ("wy_sse_u16_k15r6", 2)])
+def test_fused_depuncturing_equals_expand_then_update(name, variant):
+    """b200v_batch_update_punctured_dev (gather inside the symbol fetch of the register / group kernels, expansion for the
+    other families) against b200v_batch_depuncture_dev + b200v_batch_update_dev and against the oracle fed with the
+    restated depunctured stream: decision vectors, metrics and decoded bytes, bit for bit."""
+    import torch
+    import ka9q_viterbi_comparison_b200 as kv
+    from test_gpu_parity import CASES
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    n_frames = 3 if K == 15 else 37
+    nbytes = 24 if K == 15 else 96
+    nbits = nbytes * 8
+    T = nbits + K - 1
+    lo, hi = o.soft_range(c)
+    fill = (lo + hi + 1) // 2
+    dt = o.sym_dtype(c)
+    sb = np.dtype(dt).itemsize
+    # three segments with different codes, the last one ragged against its code length
+    a, b = (T * R * 5 // 8) // R * R, (T * R // 4) // R * R
+    segs = [(po.PI_16, a), (po.PI_15, b), (np.array([1, 1, 0, 1, 0, 1, 1], dtype=np.uint8), T * R - a - b)]
+    data, full, tx = _punctured_batch(c, R, K, nbytes, n_frames, segs, 0.35, 77)
+    n_tx = tx.shape[1]
+    d_tx = torch.from_numpy(tx.view(np.uint8).reshape(n_frames, -1).copy()).cuda()
+    d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        dec.reset()
+        dec.set_variant(variant)
+        assert dec.set_puncturing(segs, fill) == n_tx
+        dec.decode_punctured_dev(d_tx, n_tx * sb, d_out, nbytes, nbits)
+        dec.sync()
+        assert dec.variant == variant
+        out = d_out.cpu().numpy().reshape(n_frames, nbytes)
+        decs = [dec.decisions(f, 0, T) for f in range(n_frames)]
+        mets = [dec.metrics(f) for f in range(n_frames)]
+        # the unfused route on the same instance
+        d_syms = torch.zeros(n_frames * T * R * sb, dtype=torch.uint8, device="cuda")
+        ip = op = 0
+        for code, n_out in segs:
+            ip += dec.depuncture_dev(d_tx, n_tx * sb, ip, code, d_syms, T * R * sb, op, n_out, fill)
+            op += n_out
+        d_out2 = torch.zeros_like(d_out)
+        dec.decode_dev(d_syms, T * R * sb, d_out2, nbytes, nbits)
+        dec.sync()
+        assert np.array_equal(d_out2.cpu().numpy().reshape(n_frames, nbytes), out)
+        for f in (0, n_frames - 1):
+            assert np.array_equal(dec.decisions(f, 0, T), decs[f])
+        # host entry: only the transmitted symbols are handed over
+        assert np.array_equal(dec.decode_punctured(tx, nbits), out)
+        # a second pattern replaces the first; none = error
+        dec.set_puncturing(None)
+        with pytest.raises(kv.B200ViterbiError):
+            dec.update_punctured_dev(d_tx, n_tx * sb)
+    for f in range(n_frames):
+        ip, parts = 0, []
+        for code, n_out in segs:
+            s, used = po.depuncture(tx[f, ip:], code, n_out, fill, R)
+            parts.append(s[:n_out]); ip += used
+        want = np.concatenate(parts)
+        q = o.Oracle(c, T)
+        qo, qd = q.decode(want, nbits)
+        assert np.array_equal(decs[f], qd), f
+        assert np.array_equal(mets[f], q.metrics()), f
+        assert np.array_equal(out[f], qo), f
+        q.close()
+    assert np.array_equal(out[0], data[0])                     # the noiseless frame decodes to the data
+
+
+@pytest.mark.gpu
+def test_pipelined_punctured_host_decode():
+    """b200v_batch_decode_punctured on a batch large enough for the chunk pipeline (copy / compute overlap): equals the
+    full-rate b200v_batch_decode of the expanded symbols; rate 3/4 of a rate-1/4 mother code as DAB's PI_16."""
+    import torch
+    import ka9q_viterbi_comparison_b200 as kv
+    codec, K, R = kv.WY_U8, 7, 4
+    poly = [109, 79, 83, 109]
+    n_frames, nbytes = 9000, 32
+    nbits = nbytes * 8
+    T = nbits + K - 1
+    segs = [(po.PI_16, T * R)]
+    c = o.codec_wy(8, K, R, poly)
+    amp_q8, sigma_q8, mean_q8, lo, hi = o.channel_params(c, 0.4)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R, poly=poly) as dec:
+        d_syms = torch.zeros(n_frames * T * R, dtype=torch.uint8, device="cuda")
+        dec.generate_dev(d_syms, T * R, None, 0, nbits, 5, 0, amp_q8, sigma_q8, mean_q8, lo, hi)
+        dec.sync()
+        full = d_syms.cpu().numpy().view(np.int8).reshape(n_frames, T * R)
+        keep = np.resize(po.PI_16.astype(bool), T * R)
+        tx = np.ascontiguousarray(full[:, keep])
+        erased = full.copy()
+        erased[:, ~keep] = 0
+        assert dec.set_puncturing(segs, 0) == tx.shape[1]
+        assert dec.variant == 2
+        got = dec.decode_punctured(tx, nbits)
+        want = dec.decode(erased, nbits)
+        assert np.array_equal(got, want)
+        for f in (0, 4999, n_frames - 1):
+            q = o.Oracle(c, T)
+            qo, _ = q.decode(erased[f], nbits)
+            assert np.array_equal(got[f], qo), f
+            q.close()
