@@ -211,6 +211,12 @@ b200v_batch* b200v_stream_batch(b200v_stream* s);
 int b200v_batch_get_decisions(b200v_batch* h, int frame, int step0, int nsteps, uint8_t* out);
 /* Current path metrics of one frame: S elements of b200v_codec_metric_bytes() each. Host buffer. */
 int b200v_batch_get_metrics(b200v_batch* h, int frame, void* out);
+/* Per frame: the sum of the minima that renormalisations subtracted since the last init -- what the williamyang decoders'
+ * update<sum_error_t>() returns and their callers add to get_error() (viterbi_decoder_sse_u8.h:57-69;
+ * run_snr_ber.cpp:369-371, run_punctured_decoder.cpp:176, run_simple.cpp:78-79). Defined the same way for every policy
+ * that renormalises (ka9q s16: min - SHRT_MIN per renormalisation); 0 for the modular ka9q policy. Copies n_frames
+ * uint64 to the host; synchronises the stream. */
+int b200v_batch_accumulated_error(b200v_batch* h, uint64_t* out);
 /* Trellis steps consumed since the last init (the reference's dp / m_current_decoded_bit cursor). */
 int b200v_batch_steps_done(const b200v_batch* h);
 

@@ -79,6 +79,7 @@ __global__ void acs_generic_kernel(const GenericArgs a, const int tpf, const int
     __syncthreads();
 
     const int iters = (H + tpf - 1) / tpf;
+    unsigned long long rsum = 0;   // minima subtracted by this launch's renormalisations (thread 0 of the frame)
     int cur = 0;   // which metric buffer is "old"
     for (int t = 0; t < a.nsteps; t++) {
         const int pb = t & 1;
@@ -123,6 +124,7 @@ __global__ void acs_generic_kernel(const GenericArgs a, const int tpf, const int
             const int m0 = PolicyTraits<POLICY>::is_signed16 ? (int)(int16_t)newm[0] : (int)newm[0];
             if (renorm_needed<POLICY>(c, m0)) {
                 const int mn = frame_min<POLICY, WARP_FRAME>(newm, S, lt, tpf, s_scratch);
+                rsum += renorm_amount<POLICY>(mn);
                 for (int i = lt; i < S; i += tpf) {
                     const int v = PolicyTraits<POLICY>::is_signed16 ? (int)(int16_t)newm[i] : (int)newm[i];
                     newm[i] = (uint16_t)renorm_apply<POLICY>(v, mn);
@@ -142,6 +144,7 @@ __global__ void acs_generic_kernel(const GenericArgs a, const int tpf, const int
     if (live) {
         const uint16_t* fin = s_met + cur * S;
         for (int i = lt; i < S; i += tpf) g_met[i] = fin[i];
+        if (lt == 0 && a.err && rsum) a.err[frame] += rsum;
     }
 }
 

@@ -114,6 +114,7 @@ struct GrpArgs {
     int C, thr, soft_hi, soft_lo;
     int one;                       // 1 (a multiplier ptxas cannot fold: keeps the lo-path adds on the FMA pipe)
     int two;                       // 2 (multiplier of the decision fold, opaque to ptxas: keeps it an IMAD on the FMA pipe)
+    unsigned long long* err;       // [n_frames] or nullptr: += the minima this launch's renormalisations subtract
     const int* pidx; int fill;     // fused depuncturing (kernels.h): gather table of this launch's full-rate symbols, erasure value
 };
 
@@ -246,6 +247,7 @@ struct FrameState {
     uint32_t clamp;    // packed clamp operand of the saturating adds
     int skip;          // DEFER: steps that need no trigger check (uniform over the frame)
     int skip_cap;      // DEFER: bound that keeps min(w) + spread inside the 16-bit window between rebases
+    unsigned long long rsum;   // minima subtracted by the renormalisations of this launch (reference: update()'s return value)
 };
 
 template <int POLICY, class CF>
@@ -260,7 +262,7 @@ __device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint
     const int tb0 = (int)g0 + fs.base;
     const int thr = a.thr + (CF::s16 ? 32768 : 0);
     const bool need = CF::strict ? (tb0 > thr) : (tb0 >= thr);
-    if (need) fs.base = -(int)gmin;
+    if (need) { fs.rsum += (unsigned)((int)gmin + fs.base); fs.base = -(int)gmin; }    // true minimum = gmin + base
     if (gmin > CF::TH) {       // uniform over the frame
         const uint32_t sub = gmin * 0x10001u;
 #pragma unroll
@@ -678,6 +680,7 @@ acs_grp_kernel(const GrpArgs a) {
     }
     FrameState fs;
     fs.base = 0;
+    fs.rsum = 0;
     fs.clamp = CF::modular ? (uint32_t)a.two : 0u;      // modular policy: no clamp; the slot carries the fold's multiplier 2
     fs.skip = 0;
     {   // min(w) <= TH + skip * bm_max between rebases; window: that + (K + 1) branch metrics of spread and headroom
@@ -767,6 +770,7 @@ acs_grp_kernel(const GrpArgs a) {
     for (int q = 0; q < NREG; q++)
         asm volatile("st.shared.u32 [%0], %1;" :: "r"(met_addr + (uint32_t)(q * CF::TPF + tx) * 4u), "r"(w[q]) : "memory");
     if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
+    if (live && tx == 0 && a.err && fs.rsum) a.err[frame] += fs.rsum;
     if (live) {
         const uint16_t* raw = reinterpret_cast<const uint16_t*>(met_ptr);
         for (unsigned n = (unsigned)tx; n < (unsigned)CF::S; n += CF::TPF) {
@@ -855,10 +859,10 @@ int grp_threads_per_frame(const CodecParams& c) { return 1 << (c.K - 1 - grp::NL
 
 cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                           int frame0, int count, cudaStream_t st, const int* pidx, int fill) {
+                           int frame0, int count, cudaStream_t st, const int* pidx, int fill, unsigned long long* err) {
     if (count <= 0 || nsteps <= 0) return cudaSuccess;
     grp::GrpArgs a;
-    a.pidx = pidx; a.fill = fill;
+    a.pidx = pidx; a.fill = fill; a.err = err;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;

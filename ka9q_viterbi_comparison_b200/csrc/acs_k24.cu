@@ -35,6 +35,7 @@ struct K24Args {
     unsigned poly0, poly1;
     int S, thr;
     int C, soft_hi, soft_lo;         // williamyang policies: max_error and the two soft-decision levels
+    unsigned long long* err;         // [n_frames] or nullptr: += every adjustment applied (the reference's update() return value)
 };
 
 // metric as an integer: signed for the ka9q s16 policy, unsigned for the williamyang policies
@@ -63,6 +64,7 @@ __global__ void __launch_bounds__(K24_THREADS) acs_k24_kernel(const K24Args a) {
     const uint16_t* old_f = a.old_m + (size_t)frame * a.S;
     uint16_t* new_f = a.new_m + (size_t)frame * a.S;
     const int adj = pending_adjust<POLICY>(old_f, a.gmin_prev, frame, a.thr);
+    if (adj != 0 && a.err && blockIdx.x == 0 && threadIdx.x == 0) a.err[frame] += (unsigned)adj;
 
     int s0, s1;
     int e00 = 0, e01 = 0, e10 = 0, e11 = 0;          // williamyang: |sat(bt - s_i)| for bt = lo / hi, symbol i
@@ -135,9 +137,14 @@ __global__ void __launch_bounds__(K24_THREADS) acs_k24_kernel(const K24Args a) {
 // apply a pending renormalisation in place (after the last step of an update call). Each frame's trigger is
 // evaluated from a snapshot taken BEFORE any element is modified (snapshot_k24_kernel), so blocks do not race.
 template <int POLICY>
-__global__ void snapshot_k24_kernel(const uint16_t* m, const int* gmin_prev, int* adj_out, int S, int thr, int n_frames) {
+__global__ void snapshot_k24_kernel(const uint16_t* m, const int* gmin_prev, int* adj_out, int S, int thr, int n_frames,
+                                    unsigned long long* err) {
     const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f < n_frames) adj_out[f] = pending_adjust<POLICY>(m + (size_t)f * S, gmin_prev, f, thr);
+    if (f < n_frames) {
+        const int adj = pending_adjust<POLICY>(m + (size_t)f * S, gmin_prev, f, thr);
+        adj_out[f] = adj;
+        if (adj != 0 && err) err[f] += (unsigned)adj;
+    }
 }
 __global__ void renorm_k24_kernel(uint16_t* m, const int* adj_in, int S) {
     const int frame = blockIdx.y;
@@ -164,7 +171,8 @@ __global__ void fill_int_kernel(int* p, int n, int v) {
 template <int POLICY>
 static cudaError_t enqueue_k24_policy(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                                uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
-                               int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st) {
+                               int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st,
+                               unsigned long long* err) {
     const int S = c.S;
     const size_t row_u16 = (size_t)S / 16;
     const int total = nsteps * n_frames;
@@ -182,14 +190,14 @@ static cudaError_t enqueue_k24_policy(const CodecParams& c, const void* syms, si
         a.gmin_cur = gmin + (size_t)t * n_frames;
         a.poly0 = (unsigned)c.poly[0]; a.poly1 = (unsigned)c.poly[1];
         a.S = S; a.thr = c.renorm_threshold;
-        a.C = c.max_error; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo;
+        a.C = c.max_error; a.soft_hi = c.soft_hi; a.soft_lo = c.soft_lo; a.err = err;
         acs_k24_kernel<POLICY><<<grid, K24_THREADS, 0, st>>>(a);
         (*launches)++;
         *cur ^= 1;
     }
     // pending renormalisation of the last step
     snapshot_k24_kernel<POLICY><<<(n_frames + 127) / 128, 128, 0, st>>>(bufs[*cur], gmin + (size_t)(nsteps - 1) * n_frames, adj,
-                                                                 S, c.renorm_threshold, n_frames);
+                                                                 S, c.renorm_threshold, n_frames, err);
     renorm_k24_kernel<<<dim3(148 * 4, (unsigned)n_frames), 256, 0, st>>>(bufs[*cur], adj, S);
     (*launches) += 2;
     return cudaGetLastError();
@@ -197,17 +205,18 @@ static cudaError_t enqueue_k24_policy(const CodecParams& c, const void* syms, si
 
 static cudaError_t enqueue_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                                uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
-                               int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st) {
+                               int* gmin, int* adj, int n_frames, long long* launches, cudaStream_t st,
+                               unsigned long long* err) {
     switch (c.policy) {
     case P_KA9Q_S16_224:
         return enqueue_k24_policy<P_KA9Q_S16_224>(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1,
-                                                  cur, gmin, adj, n_frames, launches, st);
+                                                  cur, gmin, adj, n_frames, launches, st, err);
     case P_WY_U8:
         return enqueue_k24_policy<P_WY_U8>(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur,
-                                           gmin, adj, n_frames, launches, st);
+                                           gmin, adj, n_frames, launches, st, err);
     case P_WY_U16:
         return enqueue_k24_policy<P_WY_U16>(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur,
-                                            gmin, adj, n_frames, launches, st);
+                                            gmin, adj, n_frames, launches, st, err);
     default: return cudaErrorInvalidValue;
     }
 }
@@ -224,12 +233,12 @@ bool k24_supported(const CodecParams& c) {
 cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
                            int* gmin, int* adj, int n_frames, long long* launches, K24GraphCache* cache,
-                           cudaStream_t st) {
+                           cudaStream_t st, unsigned long long* err) {
     if (n_frames <= 0 || nsteps <= 0) return cudaSuccess;
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (!cache || cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)
         return enqueue_k24(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur, gmin, adj,
-                           n_frames, launches, st);
+                           n_frames, launches, st, err);
     const bool hit = cache->exec && cache->syms == syms && cache->sym_stride == sym_stride && cache->nsteps == nsteps &&
                      cache->step0 == step0 && cache->cur == *cur && cache->n_frames == n_frames && cache->stream == st;
     if (!hit) {
@@ -240,10 +249,10 @@ cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_st
         if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
             cudaGetLastError();
             return enqueue_k24(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur, gmin, adj,
-                               n_frames, launches, st);
+                               n_frames, launches, st, err);
         }
         const cudaError_t e1 = enqueue_k24(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1,
-                                           &cur_after, gmin, adj, n_frames, &counted, st);
+                                           &cur_after, gmin, adj, n_frames, &counted, st, err);
         const cudaError_t e2 = cudaStreamEndCapture(st, &graph);
         cudaGraphExec_t exec = nullptr;
         if (e1 != cudaSuccess || e2 != cudaSuccess || !graph ||
@@ -251,7 +260,7 @@ cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_st
             if (graph) cudaGraphDestroy(graph);
             cudaGetLastError();
             return enqueue_k24(c, syms, sym_stride, nsteps, step0, dec, dec_rows, metrics0, metrics1, cur, gmin, adj,
-                               n_frames, launches, st);
+                               n_frames, launches, st, err);
         }
         cudaGraphDestroy(graph);
         cache->exec = exec; cache->syms = syms; cache->sym_stride = sym_stride; cache->nsteps = nsteps;

@@ -117,6 +117,7 @@ struct K7Args {
     // pidx[k] = index of full-rate symbol k (counted from this launch's first step) in that stream, or < 0: not
     // transmitted, the decoder sees `fill` (puncture_code_helpers.h:17-55)
     const int* pidx; int fill;
+    unsigned long long* err;       // [n_frames] or nullptr: += the minima this launch's renormalisations subtract
 };
 
 // ---- unrolled butterfly loops (template recursion keeps every register index and bit position static) ----
@@ -259,7 +260,7 @@ struct InRegLoop<POLICY, CODE, NW> {
 // ---- one trellis step in phase P -------------------------------------------------------------------
 template <int POLICY, class CODE, int P>
 __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7Args& a, uint32_t& off,
-                                     unsigned long long* dec_out) {
+                                     unsigned long long* dec_out, uint32_t& rsum) {
     constexpr int R = CODE::R, NCW = 1 << R;
     uint32_t bm[NCW], cm[NCW];
     BmFill<POLICY, CODE, 0, NCW>::run(sym, a.C, a.soft_hi, a.soft_lo, bm, cm);
@@ -305,7 +306,7 @@ __device__ __forceinline__ void step(uint32_t (&w)[NW], const int* sym, const K7
         const uint32_t m = min(mn & 0xffffu, mn >> 16);
         const int true0 = (int)(w[0] & 0xffffu) - (int)off;
         const bool need = (POLICY == P_WY_U8 || POLICY == P_WY_U16) ? (true0 >= a.thr) : (true0 > a.thr);
-        if (need) off = m;
+        if (need) { rsum += m - off; off = m; }      // the reference subtracts the true minimum m - off
         if (Arith<POLICY>::wide && m > 4096u) {      // keep the u16 window at the bottom of the lanes
             const uint32_t sub = m * 0x10001u;
 #pragma unroll
@@ -363,10 +364,10 @@ template <int R, int SB> struct PeriodBuf {
 
 template <int POLICY, class CODE, int P>
 __device__ __forceinline__ void run_step(uint32_t (&w)[NW], const PeriodBuf<CODE::R, Arith<POLICY>::SB>& buf, const K7Args& a,
-                                         uint32_t& off, unsigned long long* dec_row) {
+                                         uint32_t& off, unsigned long long* dec_row, uint32_t& rsum) {
     int sym[CODE::R];
     buf.template symbols<POLICY>(P, sym);
-    step<POLICY, CODE, P>(w, sym, a, off, dec_row);
+    step<POLICY, CODE, P>(w, sym, a, off, dec_row, rsum);
 }
 
 // (__launch_bounds__(128, 6) for the saturating policies -- 80 registers, 8-16 bytes of spills -- measured no faster:
@@ -385,6 +386,8 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
     // ---- load canonical metrics into the phase-0 layout: register i = states (2i, 2i+1) ----
     uint32_t w[NW];
     uint32_t off = 0;
+    uint32_t rsum = 0;          // minima subtracted in the current stretch of periods (flushed into rtot every 16 periods)
+    unsigned long long rtot = 0;
     {
         const uint32_t* g = reinterpret_cast<const uint32_t*>(a.metrics + (size_t)f * S);
 #pragma unroll
@@ -431,18 +434,19 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
             else nxt.load(sp + (size_t)(pd + 1) * NB * R * SB);
         }
         unsigned long long d0, d1, d2, d3, d4, d5;
-        run_step<POLICY, CODE, 0>(w, cur, a, off, &d0);
-        run_step<POLICY, CODE, 1>(w, cur, a, off, &d1);
-        run_step<POLICY, CODE, 2>(w, cur, a, off, &d2);
-        run_step<POLICY, CODE, 3>(w, cur, a, off, &d3);
-        run_step<POLICY, CODE, 4>(w, cur, a, off, &d4);
-        run_step<POLICY, CODE, 5>(w, cur, a, off, &d5);
+        run_step<POLICY, CODE, 0>(w, cur, a, off, &d0, rsum);
+        run_step<POLICY, CODE, 1>(w, cur, a, off, &d1, rsum);
+        run_step<POLICY, CODE, 2>(w, cur, a, off, &d2, rsum);
+        run_step<POLICY, CODE, 3>(w, cur, a, off, &d3, rsum);
+        run_step<POLICY, CODE, 4>(w, cur, a, off, &d4, rsum);
+        run_step<POLICY, CODE, 5>(w, cur, a, off, &d5, rsum);
         drow[0] = d0; drow[dstride] = d1; drow[2 * dstride] = d2;
         drow[3 * dstride] = d3; drow[4 * dstride] = d4; drow[5 * dstride] = d5;
         drow += 6 * dstride;
         cur = nxt;
         // keep the 16-bit lanes from overflowing: every 16 periods rebase (uniform across the warp)
         if ((pd & 15) == 15) {
+            rtot += rsum; rsum = 0;
             if (Arith<POLICY>::modular) {
                 // subtract a multiple of 256 (keeps U mod 256): floor(min/256)*256 - 256
                 uint32_t mn = w[0];
@@ -477,11 +481,16 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
             }
         }
         unsigned long long d;
-        if (rem > 0) { run_step<POLICY, CODE, 0>(w, tb, a, off, &d); drow[0] = d; }
-        if (rem > 1) { run_step<POLICY, CODE, 1>(w, tb, a, off, &d); drow[dstride] = d; }
-        if (rem > 2) { run_step<POLICY, CODE, 2>(w, tb, a, off, &d); drow[2 * dstride] = d; }
-        if (rem > 3) { run_step<POLICY, CODE, 3>(w, tb, a, off, &d); drow[3 * dstride] = d; }
-        if (rem > 4) { run_step<POLICY, CODE, 4>(w, tb, a, off, &d); drow[4 * dstride] = d; }
+        if (rem > 0) { run_step<POLICY, CODE, 0>(w, tb, a, off, &d, rsum); drow[0] = d; }
+        if (rem > 1) { run_step<POLICY, CODE, 1>(w, tb, a, off, &d, rsum); drow[dstride] = d; }
+        if (rem > 2) { run_step<POLICY, CODE, 2>(w, tb, a, off, &d, rsum); drow[2 * dstride] = d; }
+        if (rem > 3) { run_step<POLICY, CODE, 3>(w, tb, a, off, &d, rsum); drow[3 * dstride] = d; }
+        if (rem > 4) { run_step<POLICY, CODE, 4>(w, tb, a, off, &d, rsum); drow[4 * dstride] = d; }
+    }
+
+    if (!Arith<POLICY>::modular && a.err) {
+        rtot += rsum;
+        if (rtot) a.err[f] += rtot;
     }
 
     // ---- store canonical metrics: logical state n sits at physical_of(rem, n) ----
@@ -555,10 +564,10 @@ bool k7_supported(const CodecParams& c) {
 
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st, const int* pidx, int fill) {
+                          int frame0, int count, cudaStream_t st, const int* pidx, int fill, unsigned long long* err) {
     if (count <= 0 || nsteps <= 0) return cudaSuccess;
     k7::K7Args a;
-    a.pidx = pidx; a.fill = fill;
+    a.pidx = pidx; a.fill = fill; a.err = err;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;
     a.dec = dec; a.row_phase = row_phase; a.metrics = metrics; a.n_frames = n_frames;
     a.frame0 = frame0; a.count = count;

@@ -72,6 +72,7 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
     if (PolicyTraits<POLICY>::is_signed16) { lo = (int16_t)lo; hi = (int16_t)hi; }
     const unsigned cw = a.cw[lane];                                // code word of butterfly `lane` (host table)
     const unsigned char* sp = (const unsigned char*)a.syms + (size_t)frame * a.sym_stride;
+    unsigned long long rsum = 0;     // minima subtracted by this launch's renormalisations (uniform over the warp)
     uint32_t* drow = a.dec + ((size_t)frame * a.dec_rows + a.step0) * 2;
     const int src0 = lane >> 1, src1 = 16 + (lane >> 1);
     const bool odd = lane & 1;
@@ -119,6 +120,7 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
                 const int m0 = __shfl_sync(0xffffffffu, lo, 0);
                 if (renorm_needed<POLICY>(c, m0)) {                     // uniform over the warp
                     const int mn = __reduce_min_sync(0xffffffffu, min(lo, hi));
+                    rsum += renorm_amount<POLICY>(mn);
                     lo = renorm_apply<POLICY>(lo, mn);
                     hi = renorm_apply<POLICY>(hi, mn);
                 }
@@ -127,6 +129,7 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
 #pragma unroll
         for (int w = 0; w < WPS; w++) cur[w] = nxt[w];
     }
+    if (lane == 0 && a.err && rsum) a.err[frame] += rsum;
     gm[lane] = (uint16_t)lo;
     gm[lane + 32] = (uint16_t)hi;
 }
@@ -157,6 +160,7 @@ __global__ void __launch_bounds__(128) acs_k9_warp_kernel(const GenericArgs a) {
 #pragma unroll
     for (int b = 0; b < NBF; b++) cw[b] = a.cw[lane + 32 * b];
     const unsigned char* sp = (const unsigned char*)a.syms + (size_t)frame * a.sym_stride;
+    unsigned long long rsum = 0;     // minima subtracted by this launch's renormalisations (uniform over the warp)
     uint32_t* drow = a.dec + ((size_t)frame * a.dec_rows + a.step0) * 8;
     const int srcA = lane >> 1, srcB = 16 + (lane >> 1);
     const bool odd = lane & 1;
@@ -218,6 +222,7 @@ __global__ void __launch_bounds__(128) acs_k9_warp_kernel(const GenericArgs a) {
 #pragma unroll
                     for (int s = 1; s < NS; s++) lm = min(lm, m[s]);
                     const int mn = __reduce_min_sync(0xffffffffu, lm);
+                    rsum += renorm_amount<POLICY>(mn);
 #pragma unroll
                     for (int s = 0; s < NS; s++) m[s] = renorm_apply<POLICY>(m[s], mn);
                 }
@@ -226,6 +231,7 @@ __global__ void __launch_bounds__(128) acs_k9_warp_kernel(const GenericArgs a) {
 #pragma unroll
         for (int w = 0; w < WPS; w++) cur[w] = nxt[w];
     }
+    if (lane == 0 && a.err && rsum) a.err[frame] += rsum;
 #pragma unroll
     for (int i = 0; i < NS; i++) gm[lane + 32 * i] = (uint16_t)m[i];
 }

@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(128) acs_smallk_kernel(const GenericArgs a) {
     const int step_bytes = R * c.sym_bytes;
     uint32_t* drow = a.dec + (size_t)a.step0 * a.n_frames + frame;
     const int lim = (POLICY == P_WY_U8) ? 127 : 32767;
+    unsigned long long rsum = 0;     // minima subtracted by this launch's renormalisations
 #pragma unroll 1
     for (int t = 0; t < a.nsteps; t++) {
         const void* p = sp + (size_t)t * step_bytes;
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(128) acs_smallk_kernel(const GenericArgs a) {
             int mn = n[0];
 #pragma unroll
             for (int i = 1; i < S; i++) mn = min(mn, n[i]);
+            rsum += renorm_amount<POLICY>(mn);
 #pragma unroll
             for (int i = 0; i < S; i++) n[i] = renorm_apply<POLICY>(n[i], mn);
         }
@@ -84,6 +86,7 @@ __global__ void __launch_bounds__(128) acs_smallk_kernel(const GenericArgs a) {
     }
 #pragma unroll
     for (int i = 0; i < S; i++) gm[i] = (uint16_t)m[i];
+    if (a.err && rsum) a.err[frame] += rsum;
 }
 
 template <int POLICY, int K>

@@ -160,6 +160,7 @@ struct b200v_batch {
     uint8_t* d_cw = nullptr;
     uint8_t* d_row_phase = nullptr;   // K=7 register family: phase of the step that wrote each decision row
     int* d_results = nullptr;
+    unsigned long long* d_err = nullptr;   // per frame: sum of the minima subtracted by renormalisations since init
     unsigned* d_best = nullptr;  // per-frame best end states (b200v_batch_chainback_best_dev)
     int* d_scan = nullptr;       // wy-u16 symbol range check
     K24GraphCache k24_graph;     // K=24: captured step loop of the last update call
@@ -179,7 +180,7 @@ static void free_all(b200v_batch* h) {
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
     k24_graph_cache_release(&h->k24_graph);
     cudaFree(h->d_dec); cudaFree(h->d_metrics); cudaFree(h->d_metrics2); cudaFree(h->d_gmin); cudaFree(h->d_adj); cudaFree(h->d_cw); cudaFree(h->d_results); cudaFree(h->d_row_phase); cudaFree(h->d_scan); cudaFree(h->d_best);
-    cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage); cudaFree(h->d_pidx); cudaFree(h->d_punct_stage);
+    cudaFree(h->d_syms_stage); cudaFree(h->d_out_stage); cudaFree(h->d_pidx); cudaFree(h->d_punct_stage); cudaFree(h->d_err);
     if (h->ev_u0) cudaEventDestroy(h->ev_u0);
     if (h->ev_u1) cudaEventDestroy(h->ev_u1);
     if (h->ev_c0) cudaEventDestroy(h->ev_c0);
@@ -251,6 +252,7 @@ static int create_impl(b200v_batch* h, int starting_state) {
     CUDA_TRY(cudaMalloc(&h->d_dec, h->dec_bytes));
     CUDA_TRY(cudaMalloc(&h->d_metrics, (size_t)h->n_frames * c.S * sizeof(uint16_t)));
     CUDA_TRY(cudaMalloc(&h->d_results, (size_t)h->n_frames * sizeof(int)));
+    CUDA_TRY(cudaMalloc(&h->d_err, (size_t)h->n_frames * sizeof(unsigned long long)));
     CUDA_TRY(cudaMemsetAsync(h->d_results, 0, (size_t)h->n_frames * sizeof(int), h->stream));
 
     // code word of butterfly j: bit i = parity((2j) & poly_i) (viterbi27_sse2.cpp:61-70,
@@ -322,6 +324,7 @@ extern "C" int b200v_batch_init(b200v_batch* h, int starting_state) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     CUDA_TRY(cudaSetDevice(h->device));
     CUDA_TRY(launch_init_metrics(h->d_metrics, h->n_frames, h->c, starting_state, h->stream));
+    CUDA_TRY(cudaMemsetAsync(h->d_err, 0, (size_t)h->n_frames * sizeof(unsigned long long), h->stream));
     h->launches++;
     h->cursor = 0;
     h->cur_metrics = 0;
@@ -396,27 +399,27 @@ static int launch_update_range(b200v_batch* h, const void* d_syms, size_t stride
         if (f0 != 0 || cnt != h->n_frames) return fail(B200V_ERR_STATE, "the K=24 family works on whole batches");
         CUDA_TRY(launch_acs_k24(c, d_syms, stride, nsteps, step0, (uint32_t*)h->d_dec, h->dec_rows,
                                 h->d_metrics, h->d_metrics2, &h->cur_metrics, h->d_gmin, h->d_adj, h->n_frames,
-                                &h->launches, &h->k24_graph, st));
+                                &h->launches, &h->k24_graph, st, h->d_err));
     } else if (h->variant == 2 && h->layout == DL_GRP_INTERLEAVED) {
         CUDA_TRY(launch_acs_grp(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
-                                h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, pidx, pfill));
+                                h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, pidx, pfill, h->d_err));
         h->launches++;
     } else if (h->variant == 2 && h->layout == DL_SMALLK_INTERLEAVED) {
         GenericArgs a{};
         a.c = c; a.syms = d_syms; a.sym_stride = stride; a.nsteps = nsteps; a.step0 = step0;
         a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = 1;
-        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
+        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt; a.err = h->d_err;
         CUDA_TRY(launch_acs_smallk(a, st));
         h->launches++;
     } else if (h->variant == 2) {
         CUDA_TRY(launch_acs_k7(c, d_syms, stride, nsteps, step0, (unsigned long long*)h->d_dec,
-                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, pidx, pfill));
+                               h->d_row_phase, h->d_metrics, h->n_frames, f0, cnt, st, pidx, pfill, h->d_err));
         h->launches++;
     } else {
         GenericArgs a{};
         a.c = c; a.syms = d_syms; a.sym_stride = stride; a.nsteps = nsteps; a.step0 = step0;
         a.dec = (uint32_t*)h->d_dec; a.dec_rows = h->dec_rows; a.row_words = h->row_words;
-        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt;
+        a.metrics = h->d_metrics; a.cw = h->d_cw; a.n_frames = h->n_frames; a.frame0 = f0; a.count = cnt; a.err = h->d_err;
         if (h->variant == 3) CUDA_TRY(launch_acs_k7_warp(a, st));
         else CUDA_TRY(launch_acs_generic(a, st));
         h->launches++;
@@ -905,6 +908,14 @@ extern "C" int b200v_batch_get_metrics(b200v_batch* h, int frame, void* out) {
 }
 
 extern "C" int b200v_batch_steps_done(const b200v_batch* h) { return h ? h->cursor : 0; }
+
+extern "C" int b200v_batch_accumulated_error(b200v_batch* h, uint64_t* out) {
+    if (!h || !out) return fail(B200V_ERR_ARG, "NULL argument");
+    CUDA_TRY(cudaSetDevice(h->device));
+    CUDA_TRY(cudaMemcpyAsync(out, h->d_err, (size_t)h->n_frames * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return B200V_OK;
+}
 
 extern "C" int b200v_batch_last_kernel_ms(b200v_batch* h, float* update_ms, float* chainback_ms) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");

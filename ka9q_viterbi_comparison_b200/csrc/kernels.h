@@ -20,6 +20,7 @@ struct GenericArgs {
     const uint8_t* cw;          // device; [S/2] code word per butterfly
     int n_frames;
     int frame0, count;          // this launch works on frames [frame0, frame0 + count)
+    unsigned long long* err;    // device [n_frames] or nullptr: += the minima this launch's renormalisations subtract
 };
 struct GenericPlan { int threads_per_frame, frames_per_block, smem_bytes; };
 GenericPlan generic_plan(const CodecParams& c);
@@ -41,7 +42,10 @@ cudaError_t launch_init_metrics(uint16_t* metrics, int n_frames, const CodecPara
 bool k7_supported(const CodecParams& c);
 cudaError_t launch_acs_k7(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                           unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                          int frame0, int count, cudaStream_t st, const int* pidx = nullptr, int fill = 0);
+                          int frame0, int count, cudaStream_t st, const int* pidx = nullptr, int fill = 0,
+                          unsigned long long* err = nullptr);
+// err (every family): device [n_frames] or nullptr; each frame adds the minima its renormalisations subtracted in this
+// launch -- the reference's update<sum_error_t>() return value (viterbi_decoder_sse_u8.h:57-69).
 // pidx != nullptr: depuncturing fused into the symbol fetch -- `syms` holds only each frame's transmitted symbols and
 // pidx[k] is the position of full-rate symbol k of this launch in that stream, or < 0 for a symbol that was not transmitted
 // (the decoder then sees `fill`). The K=7 register kernels and the group kernels take it.
@@ -51,7 +55,8 @@ bool grp_supported(const CodecParams& c);
 int grp_threads_per_frame(const CodecParams& c);
 cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
-                           int frame0, int count, cudaStream_t st, const int* pidx = nullptr, int fill = 0);
+                           int frame0, int count, cudaStream_t st, const int* pidx = nullptr, int fill = 0,
+                           unsigned long long* err = nullptr);
 
 // ---- K=24 (acs_k24.cu): one launch per trellis step, ping-pong metric buffers, canonical decision rows ----
 // replay cache of the captured step loop of one update call (acs_k24.cu)
@@ -65,7 +70,7 @@ struct K24GraphCache {
 cudaError_t launch_acs_k24(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            uint32_t* dec, int dec_rows, uint16_t* metrics0, uint16_t* metrics1, int* cur,
                            int* gmin, int* adj, int n_frames, long long* launches, K24GraphCache* cache,
-                           cudaStream_t st);
+                           cudaStream_t st, unsigned long long* err = nullptr);
 void k24_graph_cache_release(K24GraphCache* cache);
 bool k24_supported(const CodecParams& c);       // K = 17 ... 24, r = 1/2: ka9q viterbi224 and the williamyang policies
 

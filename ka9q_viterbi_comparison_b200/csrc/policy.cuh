@@ -108,4 +108,11 @@ __device__ __forceinline__ int renorm_apply(int m, int mn) {
     return m - mn;
 }
 
+// What one renormalisation subtracts from every metric, given the minimum: the value the reference's update() sums up
+// and returns (sse_u8.h:57-69: total_error += renormalise(new_metrics)).
+template <int POLICY>
+__device__ __forceinline__ unsigned renorm_amount(int mn) {
+    return (unsigned)(PolicyTraits<POLICY>::is_signed16 ? mn + 32768 : mn);
+}
+
 }  // namespace b200v

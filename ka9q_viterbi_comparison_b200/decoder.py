@@ -106,6 +106,7 @@ def load_library():
         "b200v_batch_get_decisions": (i32, [vp, i32, i32, i32, vp]),
         "b200v_batch_get_metrics": (i32, [vp, i32, vp]),
         "b200v_batch_steps_done": (i32, [vp]),
+        "b200v_batch_accumulated_error": (i32, [vp, vp]),
         "b200v_batch_last_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "b200v_batch_launch_count": (C.c_longlong, [vp]),
         "b200v_batch_generate_dev": (i32, [vp, vp, sz, vp, sz, u32, u64, u64, i32, i32, i32, i32, i32]),
@@ -146,7 +147,7 @@ EXPORTED_SYMBOLS = [
     "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_decode_noalloc_dev", "b200v_batch_sync",
     "b200v_stream_create", "b200v_stream_destroy", "b200v_stream_reset", "b200v_stream_push_dev", "b200v_stream_flush_dev",
     "b200v_stream_steps", "b200v_stream_emitted", "b200v_stream_sync", "b200v_stream_batch", "b200v_batch_get_decisions",
-    "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_last_kernel_ms",
+    "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_accumulated_error", "b200v_batch_last_kernel_ms",
     "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_batch_set_puncturing", "b200v_batch_update_punctured_dev",
     "b200v_batch_decode_punctured_dev", "b200v_batch_decode_punctured", "b200v_shard_range", "b200v_sharded_create",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
@@ -324,6 +325,12 @@ class BatchDecoder:
     def metrics(self, frame):
         out = np.zeros(self.S, dtype=metric_dtype(self.codec))
         _check(self.lib.b200v_batch_get_metrics(self.h, frame, out.ctypes.data))
+        return out
+
+    def accumulated_error(self):
+        """Per frame: sum of the minima subtracted by renormalisations since init (the reference's update() return value)."""
+        out = np.zeros(self.n_frames, dtype=np.uint64)
+        _check(self.lib.b200v_batch_accumulated_error(self.h, out.ctypes.data))
         return out
 
     @property

@@ -665,3 +665,52 @@ def test_long_frames_16384_bits_block_parallel_traceback(name):
             assert int(rcs[f]) == qrc
             assert np.array_equal(dec.metrics(f), q.metrics()), f
             q.close()
+
+
+@pytest.mark.parametrize("name", ["wy_sse_u8_k7r2", "wy_sse_u16_k7r2", "wy_sse_u8_k7r3", "wy_sse_u8_k9r2", "wy_sse_u16_k9r4",
+                                  "wy_sse_u8_k15r6", "wy_sse_u16_k15r6", "wy_sse_u8_k24r2", "spiral27", "spiral49", "spiral615",
+                                  "ka9q615", "ka9q224", "ka9q27"])
+def test_accumulated_error_matches_the_oracle(name):
+    """b200v_batch_accumulated_error: the sum of the minima subtracted by renormalisations since init -- the return value
+    of the reference's update<sum_error_t>() (viterbi_decoder_sse_u8.h:57-69; the oracle's sum is pinned against the
+    compiled reference in tests/test_oracle.py) -- in every kernel family, across two update calls, cleared by init."""
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    if K == 24:
+        nbytes, n_frames = 31, 2                      # 271 steps: the K=24 policies renormalise after ~200
+    elif K == 15:
+        nbytes, n_frames = 48, 3
+    else:
+        nbytes, n_frames = 200, 9
+    T = nbytes * 8 + K - 1
+    T -= T % 2                                        # spiral codecs step in pairs
+    _, syms = make_batch(c, n_frames, nbytes, 1.0 if K >= 15 else 0.7, seed=55)
+    syms = np.ascontiguousarray(syms[:, :T * R])
+    if K == 24:                                       # an erased frame: every path gains the same, new[0] reaches the threshold
+        lo, hi = o.soft_range(c)
+        syms[0, :] = (lo + hi + 1) // 2
+    want, metrics = [], []
+    split = (T // 3) & ~1
+    for f in range(n_frames):
+        q = o.Oracle(c, T)
+        q.init(0)
+        q.update(syms[f, :split * R], split)
+        q.update(syms[f, split * R:], T - split)
+        want.append(q.renorm_sum())
+        metrics.append(q.metrics())
+        q.close()
+    if name != "ka9q27":
+        assert max(want) > 0, "the case does not renormalise"
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        for v in variants(dec):
+            dec.reset()
+            dec.set_variant(v)
+            assert not dec.accumulated_error().any()
+            dec.update(syms[:, :split * R])
+            dec.update(syms[:, split * R:])
+            got = dec.accumulated_error()
+            assert [int(x) for x in got] == want, (v, got, want)
+            for f in (0, n_frames - 1):
+                assert np.array_equal(dec.metrics(f), metrics[f]), (v, f)
+            dec.reset()
+            assert not dec.accumulated_error().any()
