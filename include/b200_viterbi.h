@@ -102,6 +102,14 @@ int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream);
  * Returns B200V_ERR_ARG if the requested family does not exist for this instance. */
 int b200v_batch_set_variant(b200v_batch* h, int variant);
 int b200v_batch_get_variant(const b200v_batch* h);
+/* WY_U16 only. The specialised u16 kernels size their 16-bit lane window for |symbol| up to about three times the
+ * soft-decision range; the reference accepts any int16. Without a promise every update of such an instance first reduces
+ * max |symbol| on the device and reads it back -- b200v_batch_update_dev then SYNCHRONISES the stream, and the host-buffer
+ * batch decode runs unpipelined. A caller that knows its symbols (a quantiser's clamp) states the bound once:
+ * updates become asynchronous again and b200v_batch_decode uses the chunk pipeline. A bound above the kernels' range
+ * selects the exact (generic) family instead. 0 withdraws the promise. Symbols beyond a promised bound give undefined
+ * metrics (never out-of-bounds accesses). */
+int b200v_batch_set_symbol_bound(b200v_batch* h, int max_abs_symbol);
 /* Traceback kernel selection. mode 0 = automatic (block-parallel speculative traceback for small and medium
  * batches, one thread per frame for large ones), 1 = always one thread per frame, 2 = block-parallel whenever
  * the frame shape allows it (nbits a multiple of 8). warmup_rows = decision rows a block walks before its own
@@ -118,7 +126,8 @@ int b200v_batch_init(b200v_batch* h, int starting_state);
  * ka9q/WY codecs continue from the previous call's position (streaming); spiral codecs restart at step 0
  * and drop an odd trailing step, exactly as the reference does.
  *   _dev : syms is a device pointer; frame f's symbols start at syms + f*frame_stride_bytes and hold
- *          nsteps*R symbols (u8, int8 or int16 per codec). Asynchronous on the stream.
+ *          nsteps*R symbols (u8, int8 or int16 per codec). Asynchronous on the stream -- except WY_U16 instances
+ *          without b200v_batch_set_symbol_bound, whose symbol range check reads one int back per update.
  *   host : syms is a host pointer with the same layout; copies in, runs, and returns after completion
  *          (the reference's callers time each call on the host, main.cpp:264-278). */
 int b200v_batch_update_dev(b200v_batch* h, const void* d_syms, size_t frame_stride_bytes, int nsteps);

@@ -163,6 +163,7 @@ struct b200v_batch {
     unsigned long long* d_err = nullptr;   // per frame: sum of the minima subtracted by renormalisations since init
     unsigned* d_best = nullptr;  // per-frame best end states (b200v_batch_chainback_best_dev)
     int* d_scan = nullptr;       // wy-u16 symbol range check
+    int sym_bound = 0;           // b200v_batch_set_symbol_bound: the caller's promise max |symbol| (0 = none: scan every update)
     K24GraphCache k24_graph;     // K=24: captured step loop of the last update call
     bool user_variant = false;   // set_variant() was called: no automatic family changes
     int tb_mode = 0, tb_warmup = 0;   // b200v_batch_set_traceback
@@ -313,6 +314,13 @@ extern "C" int b200v_batch_set_variant(b200v_batch* h, int variant) {
 }
 extern "C" int b200v_batch_get_variant(const b200v_batch* h) { return h ? h->variant : 0; }
 
+extern "C" int b200v_batch_set_symbol_bound(b200v_batch* h, int max_abs_symbol) {
+    if (!h) return fail(B200V_ERR_ARG, "NULL instance");
+    if (max_abs_symbol < 0) return fail(B200V_ERR_ARG, "negative symbol bound");
+    h->sym_bound = max_abs_symbol;
+    return B200V_OK;
+}
+
 extern "C" int b200v_batch_set_traceback(b200v_batch* h, int mode, int warmup_rows) {
     if (!h) return fail(B200V_ERR_ARG, "NULL instance");
     if (mode < 0 || mode > 2 || warmup_rows < 0) return fail(B200V_ERR_ARG, "traceback mode %d / warm-up %d", mode, warmup_rows);
@@ -358,7 +366,9 @@ static int wy16_symbol_limit(const CodecParams& c) {
 }
 
 // Returns 1 if every symbol of this update is inside the specialised kernels' range, 0 if not, < 0 on error.
+// With a symbol bound promised by the caller (b200v_batch_set_symbol_bound) nothing is scanned and nothing synchronises.
 static int wy16_symbols_in_range(b200v_batch* h, const void* d_syms, size_t stride_bytes, int per_frame) {
+    if (h->sym_bound > 0) return h->sym_bound <= wy16_symbol_limit(h->c) ? 1 : 0;
     if (!h->d_scan) CUDA_TRY(cudaMalloc(&h->d_scan, sizeof(int)));
     CUDA_TRY(cudaMemsetAsync(h->d_scan, 0, sizeof(int), h->stream));
     const size_t total = (size_t)per_frame * h->n_frames;
@@ -586,7 +596,11 @@ static int decode_host(b200v_batch* h, const void* syms, uint8_t* data, unsigned
     const size_t irow = punct ? (size_t)h->punct_tx * c.sym_bytes : srow; // bytes per frame that cross PCIe
     const size_t orow = (nbits + 7) / 8;
     const int min_chunk = 2048;
-    if (h->layout == DL_CANONICAL || c.policy == P_WY_U16 || h->n_frames < 2 * min_chunk || orow == 0) {
+    // wy-u16: the specialised kernels need in-range symbols; host symbols can only be scanned after the copy, so the
+    // chunk pipeline is open to wy-u16 instances whose caller promised a bound (b200v_batch_set_symbol_bound)
+    const bool wy16_unchecked = c.policy == P_WY_U16 && !(h->sym_bound > 0 && h->sym_bound <= wy16_symbol_limit(c) &&
+                                                          (!punct || abs(h->punct_fill) <= wy16_symbol_limit(c)));
+    if (h->layout == DL_CANONICAL || wy16_unchecked || h->n_frames < 2 * min_chunk || orow == 0) {
         int rc = b200v_batch_init(h, 0);
         if (rc) return rc;
         if (punct) {

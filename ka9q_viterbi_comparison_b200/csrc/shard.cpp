@@ -88,5 +88,11 @@ extern "C" int b200v_sharded_decode(b200v_sharded* s, const void* syms, uint8_t*
     for (std::thread& t : th) t.join();
     for (size_t g = 0; g < n; g++)
         if (rc[g] != B200V_OK) { s->error = "shard " + std::to_string(g) + ": " + msg[g]; return rc[g]; }
+    // pageable buffers work, but the driver stages every chunk copy synchronously: no copy / compute overlap, and the
+    // shards' copies serialise in the driver. Not an error -- the note is what b200v_sharded_last_error() returns.
+    s->error.clear();
+    if (!b200v_host_is_pinned(syms) || (data && !b200v_host_is_pinned(data)))
+        s->error = "note: pageable host buffers -- copies were staged synchronously; allocate them with "
+                   "b200v_host_alloc_pinned (or cudaHostRegister them) for the pipelined rate";
     return B200V_OK;
 }

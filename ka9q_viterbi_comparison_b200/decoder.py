@@ -81,6 +81,7 @@ def load_library():
         "b200v_batch_set_stream": (i32, [vp, vp]),
         "b200v_batch_set_variant": (i32, [vp, i32]),
         "b200v_batch_set_traceback": (i32, [vp, i32, i32]),
+        "b200v_batch_set_symbol_bound": (i32, [vp, i32]),
         "b200v_batch_get_variant": (i32, [vp]),
         "b200v_batch_init": (i32, [vp, i32]),
         "b200v_batch_update_dev": (i32, [vp, vp, sz, i32]),
@@ -142,7 +143,7 @@ def load_library():
 EXPORTED_SYMBOLS = [
     "b200v_version", "b200v_last_error", "b200v_device_count", "b200v_codec_shape",
     "b200v_codec_symbol_bytes", "b200v_codec_metric_bytes", "b200v_batch_create", "b200v_batch_destroy",
-    "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_set_traceback", "b200v_batch_init",
+    "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_set_traceback", "b200v_batch_set_symbol_bound", "b200v_batch_init",
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
     "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_decode_noalloc_dev", "b200v_batch_sync",
     "b200v_stream_create", "b200v_stream_destroy", "b200v_stream_reset", "b200v_stream_push_dev", "b200v_stream_flush_dev",
@@ -299,6 +300,10 @@ class BatchDecoder:
 
     def set_variant(self, variant):
         _check(self.lib.b200v_batch_set_variant(self.h, variant))
+
+    def set_symbol_bound(self, max_abs_symbol):
+        """WY_U16: promise max |symbol| so that updates skip the device-side range scan (and stay asynchronous)."""
+        _check(self.lib.b200v_batch_set_symbol_bound(self.h, max_abs_symbol))
 
     def set_traceback(self, mode=0, warmup_rows=0):
         """0 = automatic, 1 = one thread per frame, 2 = block-parallel speculative traceback (verified: bit-exact)."""

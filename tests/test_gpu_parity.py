@@ -714,3 +714,41 @@ def test_accumulated_error_matches_the_oracle(name):
                 assert np.array_equal(dec.metrics(f), metrics[f]), (v, f)
             dec.reset()
             assert not dec.accumulated_error().any()
+
+
+def test_wy_u16_symbol_bound_promise_keeps_updates_asynchronous_and_pipelined():
+    """b200v_batch_set_symbol_bound: with the caller's promise the per-update range scan (and its host synchronisation)
+    is skipped and the host-buffer decode uses the chunk pipeline; results are unchanged. A promise beyond the
+    specialised kernels' range selects the exact family."""
+    import torch
+    name = "wy_sse_u16_k7r2"
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    nbytes, n_frames = 16, 9000
+    nbits, T = nbytes * 8, nbytes * 8 + K - 1
+    amp_q8, sigma_q8, mean_q8, lo, hi = o.channel_params(c, 0.7)
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        d_syms = torch.zeros(n_frames * T * R * 2, dtype=torch.uint8, device="cuda")
+        dec.generate_dev(d_syms, T * R * 2, None, 0, nbits, 7, 0, amp_q8, sigma_q8, mean_q8, lo, hi)
+        dec.sync()
+        syms = d_syms.cpu().numpy().view(np.int16).reshape(n_frames, T * R)
+        want = dec.decode(syms, nbits)                     # scanned, unpipelined
+        n0 = dec.launch_count
+        dec.set_symbol_bound(127)
+        got = dec.decode(syms, nbits)
+        assert np.array_equal(got, want)
+        assert dec.launch_count - n0 > 4                   # init + (update + chainback) per chunk: the pipeline ran
+        assert dec.variant == 2
+        dec.set_symbol_bound(30000)                        # legal input for the reference, outside the lane window
+        dec.reset()
+        dec.update_dev(d_syms, T * R * 2, T)
+        assert dec.variant in (1, 3)
+        d_out = torch.zeros(n_frames * nbytes, dtype=torch.uint8, device="cuda")
+        dec.chainback_dev(d_out, nbytes, nbits)
+        dec.sync()
+        assert np.array_equal(d_out.cpu().numpy().reshape(n_frames, nbytes), want)
+    for f in (0, n_frames - 1):
+        q = o.Oracle(c, T)
+        qo, _ = q.decode(syms[f], nbits)
+        assert np.array_equal(want[f], qo)
+        q.close()

@@ -88,6 +88,8 @@ def test_sharded_decode_matches_single_instance(name, codec):
     with kv.ShardedDecoder(codec, T, n_frames, devices) as sd:
         assert sd.shards() == [kv.shard_range(n_frames, 3, g) for g in range(3)]
         out = sd.decode(syms, nbits)
+        # numpy arrays are pageable: the decode works and says what it cost
+        assert b"pageable" in sd.lib.b200v_sharded_last_error(sd.h)
     with kv.BatchDecoder(codec, T, n_frames) as dec:
         assert np.array_equal(out, dec.decode(syms, nbits))
     for f in (0, 100, 101, 200, 300):
