@@ -1,7 +1,9 @@
 """The drop-in boundary of SURVEY 8b: the reference's per-codec C++ API served by libb200viterbi_compat.so.
 CPU: the library exports every symbol include/ref_compat/b200_ref_compat.h declares. GPU: the reference's own
 benchmark driver (src/main.cpp, unmodified, compiled by `make -C oracle compat_main` against include/ref_compat/)
-runs all six codecs through the CUDA path and decodes its noiseless frames without bit errors."""
+runs all six codecs through the CUDA path and decodes its noiseless frames without bit errors -- the nine ka9q / spiral
+rows through the per-codec functions, the twelve williamyang rows (sse_u8, avx_u8, sse_u16, avx_u16 x three codes) through
+include/ref_compat/viterbi/, the header-compatible ViterbiDecoder_Core over the C-ABI."""
 import json
 import os
 import re
@@ -54,3 +56,23 @@ def test_reference_main_runs_on_the_cuda_path(tmp_path):
         if r["K"] == 24:
             continue      # chainback_viterbi224_sse2 is broken under main.cpp's calling convention in the reference too
         assert r["total_bit_errors"] == 0, (r["name"], r["K"], r["R"], r["bit_error_rate"])
+    # the williamyang rows: main.cpp instantiates ViterbiDecoder_{SSE,AVX}_{u8,u16} from the headers on its include path;
+    # main_b200 was compiled with include/ref_compat/ first, so they are the CUDA-backed classes (the binary does not
+    # contain the reference's SIMD decoders: nm shows no _mm-based update, and the rows decode without errors)
+    ours = [r for r in rows if r["name"] in ("sse_u8", "avx_u8", "sse_u16", "avx_u16")]
+    assert len(ours) == len(rows) - 9 and len(ours) >= 12, [(r["name"], r["K"], r["R"]) for r in rows]
+    for r in ours:
+        assert r["total_samples"] >= 2
+        assert r["total_bit_errors"] == 0, (r["name"], r["K"], r["R"], r["bit_error_rate"])
+
+
+def test_compat_headers_shadow_the_williamyang_decoders():
+    """include/ref_compat/viterbi/ provides every williamyang header src/main.cpp includes for its decoders, and none of
+    them contains SIMD intrinsics: the classes forward to the C-ABI."""
+    base = os.path.join(ROOT, "include", "ref_compat", "viterbi")
+    need = ["viterbi_branch_table.h", "viterbi_decoder_core.h", "x86/viterbi_decoder_sse_u8.h", "x86/viterbi_decoder_avx_u8.h",
+            "x86/viterbi_decoder_sse_u16.h", "x86/viterbi_decoder_avx_u16.h"]
+    for n in need:
+        text = open(os.path.join(base, n)).read()
+        assert "_mm" not in text and "immintrin" not in text, n
+    assert "b200v_batch_update" in open(os.path.join(base, "viterbi_decoder_core.h")).read()

@@ -86,11 +86,15 @@ def main():
         fused_ms = dec.last_kernel_ms()[0]
         d_exp = torch.zeros(frames * srow, dtype=torch.uint8, device="cuda")
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-        st = torch.cuda.current_stream()
+        st = torch.cuda.Stream()           # a non-default stream: a NULL handle means "the instance's own stream" to the library
+        torch.cuda.synchronize()
         dec.set_stream(st.cuda_stream)
-        ev[0].record()
-        dec.depuncture_dev(d_tx, irow, 0, code, d_exp, srow, 0, T * R, fill)
-        ev[1].record(); torch.cuda.synchronize()
+        with torch.cuda.stream(st):
+            dec.depuncture_dev(d_tx, irow, 0, code, d_exp, srow, 0, T * R, fill)       # warm-up
+            ev[0].record()
+            dec.depuncture_dev(d_tx, irow, 0, code, d_exp, srow, 0, T * R, fill)
+            ev[1].record()
+        torch.cuda.synchronize()
         expand_ms = ev[0].elapsed_time(ev[1])
         dec.decode_dev(d_exp, srow, d_out, orow, nbits); dec.sync()
         plain_ms = dec.last_kernel_ms()[0]
