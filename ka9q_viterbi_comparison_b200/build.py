@@ -59,7 +59,8 @@ def build_library(force=False, verbose=False):
     # one object per source, compiled in parallel and reused while it is newer than every header and its source
     from concurrent.futures import ThreadPoolExecutor
     os.makedirs(OBJ_DIR, exist_ok=True)
-    hdr_time = max([os.path.getmtime(p) for p in _deps() if p.endswith((".cuh", ".h", ".hpp"))] +
+    # acs_grp.cu counts as a header: acs_grp_punct.cu includes it
+    hdr_time = max([os.path.getmtime(p) for p in _deps() if p.endswith((".cuh", ".h", ".hpp", "acs_grp.cu"))] +
                    [os.path.getmtime(os.path.abspath(__file__))])
     compile_flags = [f for f in NVCC_FLAGS if f != "-shared"]
 

@@ -27,6 +27,14 @@
 
 #include <type_traits>
 
+// This file is compiled twice: as itself (the kernels that read full-rate symbols, and the family's host functions) and
+// through acs_grp_punct.cu with GRP_PUNCT_TU = 1 (the kernels whose symbol fetch gathers through a puncturing table,
+// launch_acs_grp_punct only). PUNCT is a template parameter of everything that differs, so the two sets of
+// instantiations have different names.
+#ifndef GRP_PUNCT_TU
+#define GRP_PUNCT_TU 0
+#endif
+
 namespace b200v {
 namespace grp {
 
@@ -125,11 +133,12 @@ __device__ __forceinline__ int ld_symbol(const unsigned char* step_ptr, int i) {
     if (POLICY == P_WY_U8) return (int)(int8_t)__ldg(step_ptr + i);
     return (int)__ldg(step_ptr + i);
 }
-// symbol i of step t of the launch: straight from the full-rate stream, or gathered from the transmitted stream through
-// the puncturing table (block-uniform branch; `sp` is the frame's symbol base in either case)
-template <int POLICY, int R, int SB>
+// symbol i of step t of the launch: straight from the full-rate stream, or (PUNCT kernels, instantiated in
+// acs_grp_punct.cu) gathered from the transmitted stream through the puncturing table; `sp` is the frame's symbol base in
+// either case. A run-time switch here cost the r = 1/4 kernels 17 % (spiral49 27.4 -> 33.8 ms): compile-time.
+template <int POLICY, int R, int SB, bool PUNCT>
 __device__ __forceinline__ int ld_step_symbol(const GrpArgs& a, const unsigned char* sp, int t, int i) {
-    if (a.pidx) {
+    if (PUNCT) {
         const int ix = __ldg(a.pidx + t * R + i);
         if (ix < 0) return POLICY == P_WY_U16 ? (int)(int16_t)a.fill : POLICY == P_WY_U8 ? (int)(int8_t)a.fill : (a.fill & 255);
         return ld_symbol<POLICY>(sp, ix);
@@ -247,7 +256,10 @@ struct FrameState {
     uint32_t clamp;    // packed clamp operand of the saturating adds
     int skip;          // DEFER: steps that need no trigger check (uniform over the frame)
     int skip_cap;      // DEFER: bound that keeps min(w) + spread inside the 16-bit window between rebases
-    unsigned long long rsum;   // minima subtracted by the renormalisations of this launch (reference: update()'s return value)
+    // minima subtracted by the renormalisations of this launch (reference: update()'s return value): 8-bit policies sum
+    // in 32 bits (255 per renormalisation: exact for 16 M steps per launch), 16-bit policies in 64
+    uint32_t rsum32;
+    unsigned long long rsum;
 };
 
 template <int POLICY, class CF>
@@ -262,7 +274,11 @@ __device__ __forceinline__ void renorm(uint32_t (&w)[NREG], FrameState& fs, uint
     const int tb0 = (int)g0 + fs.base;
     const int thr = a.thr + (CF::s16 ? 32768 : 0);
     const bool need = CF::strict ? (tb0 > thr) : (tb0 >= thr);
-    if (need) { fs.rsum += (unsigned)((int)gmin + fs.base); fs.base = -(int)gmin; }    // true minimum = gmin + base
+    if (need) {      // true minimum = gmin + base
+        if (CF::TOP == 255) fs.rsum32 += (unsigned)((int)gmin + fs.base);
+        else fs.rsum += (unsigned)((int)gmin + fs.base);
+        fs.base = -(int)gmin;
+    }
     if (gmin > CF::TH) {       // uniform over the frame
         const uint32_t sub = gmin * 0x10001u;
 #pragma unroll
@@ -484,7 +500,7 @@ __device__ __forceinline__ int bm_post(int sum) {
 // Cooperative table build for TPF = 4 (K=9): per step, each of the frame's four threads evaluates NCW/4 code
 // words as subset sums of the per-symbol costs, fetches the lane-1 partner (code word ^ D_s) with one shuffle
 // and writes its NCW/4 entries. ~4x fewer instructions than one bm_eval per code word and task.
-template <int POLICY, class CODE, class CF>
+template <int POLICY, class CODE, class CF, bool PUNCT>
 __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl) {
     constexpr int R = CF::R, NPT = CF::NCW / 4, LOGN = (NPT == 1 ? 0 : NPT == 2 ? 1 : NPT == 4 ? 2 : NPT == 8 ? 3 : 4);
     static_assert(CF::TPF == 4 && CF::NCW >= 4 && (1 << LOGN) == NPT, "four threads per frame, NCW/4 code words each");
@@ -498,7 +514,7 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
         int v0[R], v1[R];
 #pragma unroll
         for (int i = 0; i < R; i++) {
-            const int sym = ld_step_symbol<POLICY, R, CF::SB>(a, sp, t, i);
+            const int sym = ld_step_symbol<POLICY, R, CF::SB, PUNCT>(a, sp, t, i);
             symbol_costs<POLICY>(sym, a, v0[i], v1[i]);
         }
         // code words of this thread: c = tx * NPT + j; the two top bits of c come from tx
@@ -528,11 +544,11 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
 // ---- branch-metric tables of one group of five steps ---------------------------------------------------
 // entry (s, c) = { pack(bm[c], bm[c ^ D_s]), pack(cm[c], cm[c ^ D_s]) }, D_s = code-word difference between the
 // two lanes of a register in phase s. One task computes bm of c and c ^ D_s once and writes both entries.
-template <int POLICY, class CODE, class CF>
+template <int POLICY, class CODE, class CF, bool PUNCT>
 __device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl) {
     constexpr int R = CF::R, HALF = CF::NCW / 2;
     if constexpr (CF::TPF == 4 && CF::NCW >= 4) {
-        fill_tables_coop<POLICY, CODE, CF>(a, sp, g, tab_addr, tx, fl);
+        fill_tables_coop<POLICY, CODE, CF, PUNCT>(a, sp, g, tab_addr, tx, fl);
         return;
     }
     const uint32_t buf = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
@@ -546,7 +562,7 @@ __device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned cha
         else { c1 = (unsigned)idx; c2 = (unsigned)(idx + HALF); }
         int sym[R];
 #pragma unroll
-        for (int i = 0; i < R; i++) sym[i] = ld_step_symbol<POLICY, R, CF::SB>(a, sp, t, i);
+        for (int i = 0; i < R; i++) sym[i] = ld_step_symbol<POLICY, R, CF::SB, PUNCT>(a, sp, t, i);
         uint32_t b1, m1, b2, m2;
         bm_eval<POLICY, R>(c1, sym, a, b1, m1);
         bm_eval<POLICY, R>(c2, sym, a, b2, m2);
@@ -636,7 +652,7 @@ __device__ __forceinline__ void step(uint32_t (&w)[NREG], FrameState& fs, const 
 #ifndef GRP_MINB
 #define GRP_MINB 4
 #endif
-template <int POLICY, class CODE>
+template <int POLICY, class CODE, bool PUNCT>
 __global__ void __launch_bounds__((Cfg<POLICY, CODE>::THREADS), (Cfg<POLICY, CODE>::TPF >= 32 ? 3 : GRP_MINB))
 acs_grp_kernel(const GrpArgs a) {
     using CF = Cfg<POLICY, CODE>;
@@ -681,6 +697,7 @@ acs_grp_kernel(const GrpArgs a) {
     FrameState fs;
     fs.base = 0;
     fs.rsum = 0;
+    fs.rsum32 = 0;
     fs.clamp = CF::modular ? (uint32_t)a.two : 0u;      // modular policy: no clamp; the slot carries the fold's multiplier 2
     fs.skip = 0;
     {   // min(w) <= TH + skip * bm_max between rebases; window: that + (K + 1) branch metrics of spread and headroom
@@ -713,7 +730,7 @@ acs_grp_kernel(const GrpArgs a) {
     unsigned long long* drow = a.dec + ((size_t)a.step0 * a.n_frames + frame) * CF::TPF + tx;
 
     const int ngroups = (a.nsteps + NL - 1) / NL;
-    if (ngroups > 0) fill_tables<POLICY, CODE, CF>(a, sp, 0, tab_addr, tx, fl);
+    if (ngroups > 0) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, 0, tab_addr, tx, fl);
     if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
 
     // Whole groups run their five steps unconditionally: a step guarded by `if (nsub > s)` ends in a join where ptxas
@@ -738,7 +755,7 @@ acs_grp_kernel(const GrpArgs a) {
     const int nmain = UNCOND ? nfull : 0;
 #pragma unroll 1
     for (int g = 0; g < nmain; g++) {
-        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx, fl);
+        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, g + 1, tab_addr, tx, fl);
         const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
         step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
         step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);
@@ -752,7 +769,7 @@ acs_grp_kernel(const GrpArgs a) {
 #pragma unroll 1
     for (int g = nmain; g < ngroups; g++) {
         const int nsub = min(NL, a.nsteps - g * NL);
-        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF>(a, sp, g + 1, tab_addr, tx, fl);
+        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, g + 1, tab_addr, tx, fl);
         const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
         step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
         if (nsub > 1) step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);
@@ -770,7 +787,7 @@ acs_grp_kernel(const GrpArgs a) {
     for (int q = 0; q < NREG; q++)
         asm volatile("st.shared.u32 [%0], %1;" :: "r"(met_addr + (uint32_t)(q * CF::TPF + tx) * 4u), "r"(w[q]) : "memory");
     if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
-    if (live && tx == 0 && a.err && fs.rsum) a.err[frame] += fs.rsum;
+    if (live && tx == 0 && a.err && (fs.rsum | fs.rsum32)) a.err[frame] += fs.rsum + fs.rsum32;
     if (live) {
         const uint16_t* raw = reinterpret_cast<const uint16_t*>(met_ptr);
         for (unsigned n = (unsigned)tx; n < (unsigned)CF::S; n += CF::TPF) {
@@ -787,7 +804,7 @@ acs_grp_kernel(const GrpArgs a) {
 template <int POLICY, class CODE>
 static cudaError_t launch_one(const GrpArgs& a, cudaStream_t st) {
     using CF = Cfg<POLICY, CODE>;
-    auto k = acs_grp_kernel<POLICY, CODE>;
+    auto k = acs_grp_kernel<POLICY, CODE, GRP_PUNCT_TU != 0>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, CF::SMEM);
     if (e != cudaSuccess) return e;
     const int blocks = (a.count + CF::FPB - 1) / CF::FPB;
@@ -835,6 +852,7 @@ static int find_instance(const CodecParams& c) {
 
 }  // namespace grp
 
+#if !GRP_PUNCT_TU
 bool grp_supported(const CodecParams& c) {
     if (grp::find_instance(c) < 0) return false;
     // wy-u8: the clamp arithmetic assumes the reference's u8 ranges
@@ -857,10 +875,24 @@ bool grp_supported(const CodecParams& c) {
 
 int grp_threads_per_frame(const CodecParams& c) { return 1 << (c.K - 1 - grp::NL - 1); }
 
-cudaError_t launch_acs_grp(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+cudaError_t launch_acs_grp_punct(const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
+                                 unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
+                                 int frame0, int count, cudaStream_t st, const int* pidx, int fill, unsigned long long* err);
+#endif
+
+#if GRP_PUNCT_TU
+cudaError_t launch_acs_grp_punct(
+#else
+cudaError_t launch_acs_grp(
+#endif
+                           const CodecParams& c, const void* syms, size_t sym_stride, int nsteps, int step0,
                            unsigned long long* dec, uint8_t* row_phase, uint16_t* metrics, int n_frames,
                            int frame0, int count, cudaStream_t st, const int* pidx, int fill, unsigned long long* err) {
     if (count <= 0 || nsteps <= 0) return cudaSuccess;
+#if !GRP_PUNCT_TU
+    if (pidx) return launch_acs_grp_punct(c, syms, sym_stride, nsteps, step0, dec, row_phase, metrics, n_frames, frame0, count,
+                                          st, pidx, fill, err);
+#endif
     grp::GrpArgs a;
     a.pidx = pidx; a.fill = fill; a.err = err;
     a.syms = (const unsigned char*)syms; a.sym_stride = sym_stride; a.nsteps = nsteps; a.step0 = step0;

@@ -2,6 +2,10 @@
 #pragma once
 #include <stdint.h>
 
+#ifndef DPX_VOLATILE
+#define DPX_VOLATILE volatile
+#endif
+
 namespace b200v {
 
 __device__ __forceinline__ uint32_t pack2(uint32_t lo, uint32_t hi) { return lo | (hi << 16); }
@@ -13,14 +17,14 @@ template <int BIT_LO, int BIT_HI, bool NEG>
 __device__ __forceinline__ uint32_t min_acc(uint32_t a, uint32_t b, uint32_t& acc) {
     uint32_t s;
     if (NEG) {
-        asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+        asm DPX_VOLATILE("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
             "min.u16x2 %0, %2, %3;\n\t"
             "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %2;\n\t"
             "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
             "@!pv or.b32 %1, %1, %4;\n\t@!pu or.b32 %1, %1, %5;\n\t}"
             : "=&r"(s), "+r"(acc) : "r"(a), "r"(b), "n"(1u << BIT_LO), "n"(1u << BIT_HI));
     } else {
-        asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+        asm DPX_VOLATILE("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
             "min.u16x2 %0, %2, %3;\n\t"
             "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %2;\n\t"
             "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
@@ -36,7 +40,7 @@ __device__ __forceinline__ uint32_t min_acc(uint32_t a, uint32_t b, uint32_t& ac
 template <int BIT>
 __device__ __forceinline__ uint32_t min_facc(uint32_t a, uint32_t b, float& acc_lo, float& acc_hi) {
     uint32_t s;
-    asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+    asm DPX_VOLATILE("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
         "min.u16x2 %0, %3, %4;\n\t"
         "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %3;\n\t"
         "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
@@ -48,7 +52,7 @@ __device__ __forceinline__ uint32_t min_facc(uint32_t a, uint32_t b, float& acc_
 template <int BIT>
 __device__ __forceinline__ uint32_t min_facc_strict(uint32_t a, uint32_t b, float& acc_lo, float& acc_hi) {
     uint32_t s;
-    asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
+    asm DPX_VOLATILE("{\n\t.reg .pred pu, pv;\n\t.reg .u16 r0, r1, r2, r3;\n\t"
         "min.u16x2 %0, %3, %4;\n\t"
         "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %3;\n\t"
         "setp.eq.u16 pv, r0, r2;\n\tsetp.eq.u16 pu, r1, r3;\n\t"
@@ -60,7 +64,7 @@ __device__ __forceinline__ uint32_t min_facc_strict(uint32_t a, uint32_t b, floa
 template <int BIT>
 __device__ __forceinline__ uint32_t relu_neg_facc(uint32_t t, float& acc_lo, float& acc_hi) {
     uint32_t z;
-    asm volatile("{\n\t.reg .pred pu, pv;\n\t.reg .s16 r0, r1, r2, r3;\n\t"
+    asm DPX_VOLATILE("{\n\t.reg .pred pu, pv;\n\t.reg .s16 r0, r1, r2, r3;\n\t"
         "min.s16x2 %0, %3, %4;\n\t"
         "mov.b32 {r0, r1}, %0;\n\tmov.b32 {r2, r3}, %3;\n\t"
         "setp.eq.s16 pv, r0, r2;\n\tsetp.eq.s16 pu, r1, r3;\n\t"

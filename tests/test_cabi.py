@@ -52,6 +52,23 @@ def test_argument_validation_needs_no_gpu():
     assert not lib.b200v_batch_create(kv.WY_U8, 2, 2, poly, 10, 1, 0, None)       # K too small
     assert lib.b200v_batch_init(None, 0) < 0
     lib.b200v_batch_destroy(None)                                                 # accepted, like delete_*(NULL)
+    # stream geometry: chunk a multiple of 8, depth a multiple of the chunk and >= K-1, K <= 16
+    for depth, chunk, msg in ((48, 20, b"chunk"), (40, 16, b"depth"), (0, 16, b"depth")):
+        assert not lib.b200v_stream_create(kv.KA9Q27, 7, 2, poly, 4, depth, chunk, 0, None)
+        assert msg in lib.b200v_last_error()
+    poly24 = (C.c_int * 2)(0o62650457, 0o62650455)
+    assert not lib.b200v_stream_create(kv.KA9Q224, 24, 2, poly24, 1, 64, 32, 0, None)
+    assert b"K <= 16" in lib.b200v_last_error()
+    assert lib.b200v_stream_push_dev(None, None, 0, None, 0, None) < 0
+    lib.b200v_stream_destroy(None)
+    # the allocation-free entry rejects what it does not serve before it touches the device
+    poly9 = (C.c_int * 2)(0x1af, 0x11d)
+    assert lib.b200v_decode_noalloc_dev(kv.KA9Q29, 9, 2, poly9, None, 72, 4, 1, 144, 1, 8, 64, 0, None) == -1
+    assert b"K=7" in lib.b200v_last_error()
+    assert lib.b200v_decode_noalloc_dev(kv.KA9Q27, 7, 2, poly, None, 2054, 4096, 1, 4108, 1, 256, 2048, 0, None) == -1
+    assert b"B200V_NOALLOC_SCRATCH_BYTES" in lib.b200v_last_error()
+    assert lib.b200v_batch_set_puncturing(None, None, 0, 0, None) < 0
+    assert lib.b200v_batch_accumulated_error(None, None) < 0
 
 
 def test_no_cpu_fallback():
