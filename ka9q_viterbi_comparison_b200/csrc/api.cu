@@ -146,8 +146,17 @@ struct b200v_batch {
     bool generic_ok = true;      // the generic shared-memory family exists for this K
     int fast_layout = DL_BALLOT_FRAME_MAJOR;   // decision layout of the specialised family, if any
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    static constexpr int NPIPE = 4;
-    cudaStream_t pipe[NPIPE] = { nullptr, nullptr, nullptr, nullptr };   // b200v_batch_decode's chunk pipeline
+// streams of the chunk pipeline. Measured e2e, 256 Ki K=9 r=1/2 frames (copy time ~ kernel time, so the overlap shows):
+// 2 streams 11.4, 4 streams 17.5, 8 streams 24.2, 16 streams 23.6 Gbit/s; 16 / 24 / 32 / 64 chunks with 8 streams:
+// 23.9 / 23.9 / 24.2 / 20.8. The PCIe-bound K=7 batch is indifferent (27.1 Gbit/s throughout).
+#ifndef B200V_NPIPE
+#define B200V_NPIPE 8
+#endif
+#ifndef B200V_MAXCHUNKS
+#define B200V_MAXCHUNKS 32
+#endif
+    static constexpr int NPIPE = B200V_NPIPE;
+    cudaStream_t pipe[NPIPE] = {};   // b200v_batch_decode's chunk pipeline
     cudaEvent_t ev_pipe = nullptr;
     cudaEvent_t ev_u0 = nullptr, ev_u1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;
     bool timed_update = false, timed_chainback = false;
@@ -509,6 +518,7 @@ static int launch_chainback_range(b200v_batch* h, uint8_t* d_data, size_t stride
     a.nbits = nbits; a.endstate = endstate; a.endstates = endstates; a.results = h->d_results;
     // chunks of the pipelined host-buffer decode run beside other chunks' kernels and copies: throughput, not
     // latency, so they keep the per-frame kernels (measured: K=7 65536 frames e2e 17.4 vs 10.3 Gbit/s)
+    // (block-parallel traceback for the chunks of the other layouts measured slower too: K=9 e2e 17.5 -> 13.3 Gbit/s)
     a.par_mode = (pipelined && h->tb_mode == 0) ? 1 : h->tb_mode; a.par_warmup = h->tb_warmup;
     CUDA_TRY(launch_chainback(a, st));
     h->launches++;
@@ -638,7 +648,7 @@ static int decode_host(b200v_batch* h, const void* syms, uint8_t* data, unsigned
     CUDA_TRY(cudaEventRecord(h->ev_pipe, h->stream));
     const int nsteps = policy_is_spiral(c.policy) ? (h->frame_steps / 2) * 2 : h->frame_steps;
     int nchunks = h->n_frames / min_chunk;
-    if (nchunks > 32) nchunks = 32;
+    if (nchunks > B200V_MAXCHUNKS) nchunks = B200V_MAXCHUNKS;
     const int chunk = (((h->n_frames + nchunks - 1) / nchunks) + 127) / 128 * 128;
     for (int i = 0; i < b200v_batch::NPIPE; i++) CUDA_TRY(cudaStreamWaitEvent(h->pipe[i], h->ev_pipe, 0));
     int k = 0;
