@@ -427,25 +427,41 @@ __global__ void __launch_bounds__(128) acs_k7_kernel(const K7Args a) {
         if (PUNCT) cur.load_punctured(sp, a.pidx, pfill);
         else cur.load(sp);
     }
+    // Two nested loops: the rebase (every 16 periods) sits BETWEEN runs of the inner loop, not behind an `if` inside it.
+    // A conditional block in the hot loop ends in a join where ptxas brings the 32 renamed metric registers back to
+    // common places on every iteration (27 IMAD.MOV per period on the FMA-heavy pipe, the binding one: round 2, ncu
+    // source page of the ka9q27 kernel).
+#ifndef K7_NESTED_LOOP
+#define K7_NESTED_LOOP 1
+#endif
+    int pd = 0;
 #pragma unroll 1
-    for (int pd = 0; pd < periods; pd++) {
-        if (pd + 1 < periods) {
-            if (PUNCT) nxt.load_punctured(sp, a.pidx + (size_t)(pd + 1) * NB * R, pfill);
-            else nxt.load(sp + (size_t)(pd + 1) * NB * R * SB);
+    while (pd < periods) {
+        const int pend = K7_NESTED_LOOP ? min(periods, (pd | 15) + 1) : pd + 1;
+#ifndef K7_PERIOD_UNROLL
+#define K7_PERIOD_UNROLL 1
+#endif
+        constexpr int PERIOD_UNROLL = K7_PERIOD_UNROLL;
+#pragma unroll PERIOD_UNROLL
+        for (; pd < pend; pd++) {
+            if (pd + 1 < periods) {
+                if (PUNCT) nxt.load_punctured(sp, a.pidx + (size_t)(pd + 1) * NB * R, pfill);
+                else nxt.load(sp + (size_t)(pd + 1) * NB * R * SB);
+            }
+            unsigned long long d0, d1, d2, d3, d4, d5;
+            run_step<POLICY, CODE, 0>(w, cur, a, off, &d0, rsum);
+            run_step<POLICY, CODE, 1>(w, cur, a, off, &d1, rsum);
+            run_step<POLICY, CODE, 2>(w, cur, a, off, &d2, rsum);
+            run_step<POLICY, CODE, 3>(w, cur, a, off, &d3, rsum);
+            run_step<POLICY, CODE, 4>(w, cur, a, off, &d4, rsum);
+            run_step<POLICY, CODE, 5>(w, cur, a, off, &d5, rsum);
+            drow[0] = d0; drow[dstride] = d1; drow[2 * dstride] = d2;
+            drow[3 * dstride] = d3; drow[4 * dstride] = d4; drow[5 * dstride] = d5;
+            drow += 6 * dstride;
+            cur = nxt;
         }
-        unsigned long long d0, d1, d2, d3, d4, d5;
-        run_step<POLICY, CODE, 0>(w, cur, a, off, &d0, rsum);
-        run_step<POLICY, CODE, 1>(w, cur, a, off, &d1, rsum);
-        run_step<POLICY, CODE, 2>(w, cur, a, off, &d2, rsum);
-        run_step<POLICY, CODE, 3>(w, cur, a, off, &d3, rsum);
-        run_step<POLICY, CODE, 4>(w, cur, a, off, &d4, rsum);
-        run_step<POLICY, CODE, 5>(w, cur, a, off, &d5, rsum);
-        drow[0] = d0; drow[dstride] = d1; drow[2 * dstride] = d2;
-        drow[3 * dstride] = d3; drow[4 * dstride] = d4; drow[5 * dstride] = d5;
-        drow += 6 * dstride;
-        cur = nxt;
-        // keep the 16-bit lanes from overflowing: every 16 periods rebase (uniform across the warp)
-        if ((pd & 15) == 15) {
+        // keep the 16-bit lanes from overflowing: after every 16th period rebase (uniform across the warp)
+        if ((pd & 15) == 0) {
             rtot += rsum; rsum = 0;
             if (Arith<POLICY>::modular) {
                 // subtract a multiple of 256 (keeps U mod 256): floor(min/256)*256 - 256
