@@ -207,6 +207,10 @@ int b200v_stream_reset(b200v_stream* s, int starting_state);
 int b200v_stream_push_dev(b200v_stream* s, const void* d_syms, size_t sym_stride_bytes, uint8_t* d_out,
                           size_t out_stride_bytes, unsigned* bits_out);
 int b200v_stream_flush_dev(b200v_stream* s, int endstate, uint8_t* d_out, size_t out_stride_bytes, unsigned* bits_out);
+/* The same with host buffers (copies in and out, returns after completion, like the reference's synchronous calls). */
+int b200v_stream_push(b200v_stream* s, const void* syms, size_t sym_stride_bytes, uint8_t* out, size_t out_stride_bytes,
+                      unsigned* bits_out);
+int b200v_stream_flush(b200v_stream* s, int endstate, uint8_t* out, size_t out_stride_bytes, unsigned* bits_out);
 /* trellis steps consumed / bits emitted per stream since the last reset */
 long long b200v_stream_steps(const b200v_stream* s);
 long long b200v_stream_emitted(const b200v_stream* s);

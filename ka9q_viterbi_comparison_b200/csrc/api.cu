@@ -823,6 +823,53 @@ extern "C" int b200v_stream_flush_dev(b200v_stream* s, int endstate, uint8_t* d_
     return B200V_OK;
 }
 
+// host-buffer variants: copy in, push / flush on the device, copy the emitted bytes out; synchronous like the reference's calls
+extern "C" int b200v_stream_push(b200v_stream* s, const void* syms, size_t sym_stride_bytes, uint8_t* out,
+                                 size_t out_stride_bytes, unsigned* bits_out) {
+    if (!s) return fail(B200V_ERR_ARG, "NULL stream");
+    if (!syms) return fail(B200V_ERR_ARG, "NULL symbol buffer");
+    b200v_batch* h = s->b;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t row = (size_t)s->chunk * h->c.R * h->c.sym_bytes, orow = (size_t)s->chunk / 8;
+    if (h->n_frames == 1) { sym_stride_bytes = row; out_stride_bytes = orow; }
+    int rc = ensure_stage(&h->d_syms_stage, &h->syms_stage_bytes, row * h->n_frames);
+    if (rc) return rc;
+    rc = ensure_stage((void**)&h->d_out_stage, &h->out_stage_bytes, (size_t)(s->W / 8 + 1) * h->n_frames);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpy2DAsync(h->d_syms_stage, row, syms, sym_stride_bytes, row, (size_t)h->n_frames, cudaMemcpyHostToDevice, h->stream));
+    unsigned n = 0;
+    rc = b200v_stream_push_dev(s, h->d_syms_stage, row, h->d_out_stage, orow, &n);
+    if (rc) return rc;
+    if (n) {
+        if (!out) return fail(B200V_ERR_ARG, "NULL output buffer");
+        CUDA_TRY(cudaMemcpy2DAsync(out, out_stride_bytes, h->d_out_stage, orow, orow, (size_t)h->n_frames, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (bits_out) *bits_out = n;
+    return B200V_OK;
+}
+
+extern "C" int b200v_stream_flush(b200v_stream* s, int endstate, uint8_t* out, size_t out_stride_bytes, unsigned* bits_out) {
+    if (!s) return fail(B200V_ERR_ARG, "NULL stream");
+    b200v_batch* h = s->b;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t orow = (size_t)s->W / 8 + 1;
+    int rc = ensure_stage((void**)&h->d_out_stage, &h->out_stage_bytes, orow * h->n_frames);
+    if (rc) return rc;
+    unsigned n = 0;
+    rc = b200v_stream_flush_dev(s, endstate, h->d_out_stage, orow, &n);
+    if (rc) return rc;
+    if (n) {
+        if (!out) return fail(B200V_ERR_ARG, "NULL output buffer");
+        const size_t nb = (n + 7) / 8;
+        if (h->n_frames == 1) out_stride_bytes = nb;
+        CUDA_TRY(cudaMemcpy2DAsync(out, out_stride_bytes, h->d_out_stage, orow, nb, (size_t)h->n_frames, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (bits_out) *bits_out = n;
+    return B200V_OK;
+}
+
 extern "C" long long b200v_stream_steps(const b200v_stream* s) { return s ? s->steps : 0; }
 extern "C" long long b200v_stream_emitted(const b200v_stream* s) { return s ? s->emitted : 0; }
 extern "C" int b200v_stream_sync(b200v_stream* s) { return s ? b200v_batch_sync(s->b) : fail(B200V_ERR_ARG, "NULL stream"); }

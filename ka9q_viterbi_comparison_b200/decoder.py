@@ -100,6 +100,8 @@ def load_library():
         "b200v_stream_reset": (i32, [vp, i32]),
         "b200v_stream_push_dev": (i32, [vp, vp, sz, vp, sz, C.POINTER(u32)]),
         "b200v_stream_flush_dev": (i32, [vp, i32, vp, sz, C.POINTER(u32)]),
+        "b200v_stream_push": (i32, [vp, vp, sz, vp, sz, C.POINTER(u32)]),
+        "b200v_stream_flush": (i32, [vp, i32, vp, sz, C.POINTER(u32)]),
         "b200v_stream_steps": (C.c_longlong, [vp]),
         "b200v_stream_emitted": (C.c_longlong, [vp]),
         "b200v_stream_sync": (i32, [vp]),
@@ -146,7 +148,7 @@ EXPORTED_SYMBOLS = [
     "b200v_batch_set_stream", "b200v_batch_set_variant", "b200v_batch_get_variant", "b200v_batch_set_traceback", "b200v_batch_set_symbol_bound", "b200v_batch_init",
     "b200v_batch_update_dev", "b200v_batch_update", "b200v_batch_chainback_dev", "b200v_batch_chainback",
     "b200v_batch_chainback_results", "b200v_batch_chainback_best_dev", "b200v_batch_decode", "b200v_batch_decode_dev", "b200v_decode_noalloc_dev", "b200v_batch_sync",
-    "b200v_stream_create", "b200v_stream_destroy", "b200v_stream_reset", "b200v_stream_push_dev", "b200v_stream_flush_dev",
+    "b200v_stream_create", "b200v_stream_destroy", "b200v_stream_reset", "b200v_stream_push_dev", "b200v_stream_flush_dev", "b200v_stream_push", "b200v_stream_flush",
     "b200v_stream_steps", "b200v_stream_emitted", "b200v_stream_sync", "b200v_stream_batch", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_accumulated_error", "b200v_batch_last_kernel_ms",
     "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_batch_set_puncturing", "b200v_batch_update_punctured_dev",
@@ -398,6 +400,22 @@ class StreamDecoder:
         n = C.c_uint(0)
         _check(self.lib.b200v_stream_push_dev(self.h, _ptr(d_syms), sym_stride, _ptr(d_out), out_stride, C.byref(n)))
         return n.value
+
+    def push(self, syms):
+        """Host symbols [n_streams, chunk*R] -> emitted bytes [n_streams, chunk/8] (or None while the window fills)."""
+        syms = np.ascontiguousarray(syms, dtype=self.sym_dtype).reshape(self.n_streams, -1)
+        assert syms.shape[1] == self.chunk * self.R
+        out = np.zeros((self.n_streams, self.chunk // 8), dtype=np.uint8)
+        n = C.c_uint(0)
+        _check(self.lib.b200v_stream_push(self.h, syms.ctypes.data, syms.strides[0], out.ctypes.data, out.strides[0], C.byref(n)))
+        return out if n.value else None
+
+    def flush(self, endstate=-1):
+        """Remaining bits at the end of the stream: (bytes [n_streams, ceil(bits/8)], bits)."""
+        out = np.zeros((self.n_streams, (self.depth + self.chunk) // 8 + 1), dtype=np.uint8)
+        n = C.c_uint(0)
+        _check(self.lib.b200v_stream_flush(self.h, endstate, out.ctypes.data, out.strides[0], C.byref(n)))
+        return out[:, :(n.value + 7) // 8], n.value
 
     def flush_dev(self, d_out, out_stride, endstate=-1):
         n = C.c_uint(0)

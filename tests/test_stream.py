@@ -161,3 +161,29 @@ def test_stream_argument_errors():
         kv.StreamDecoder(kv.KA9Q615, 4, 8, 8)           # depth below K-1
     with pytest.raises(kv.B200ViterbiError):
         kv.StreamDecoder(kv.KA9Q224, 1, 64, 32)         # K=24 has no stream decoder
+
+
+def test_stream_host_buffer_entries_match_the_device_entries():
+    """b200v_stream_push / _flush (host buffers, synchronous) against push_dev / flush_dev on the same symbols."""
+    import torch
+    codec, K, R = kv.SPIRAL27, 7, 2
+    c = o.codec_by_name("spiral27")
+    n_streams, chunk, depth, npush = 7, 32, 64, 9
+    T = chunk * npush
+    syms = np.stack([o.make_frame(c, T // 8 + 1, 0.5, seed=3, frame=f)[1][:T * R] for f in range(n_streams)])
+    with kv.StreamDecoder(codec, n_streams, depth, chunk) as a, kv.StreamDecoder(codec, n_streams, depth, chunk) as b:
+        a.reset(0); b.reset(0)
+        d_syms = torch.from_numpy(syms.copy()).cuda()
+        d_out = torch.zeros(n_streams, (depth + chunk) // 8 + 1, dtype=torch.uint8, device="cuda")
+        for p in range(npush):
+            got = a.push(syms[:, p * chunk * R:(p + 1) * chunk * R])
+            n = b.push_dev(d_syms.data_ptr() + p * chunk * R, T * R, d_out, d_out.shape[1])
+            b.sync()
+            assert (got is None) == (n == 0)
+            if n:
+                assert np.array_equal(got, d_out.cpu().numpy()[:, :chunk // 8]), p
+        tail, nbits = a.flush()
+        n = b.flush_dev(d_out, d_out.shape[1])
+        b.sync()
+        assert nbits == n == depth
+        assert np.array_equal(tail, d_out.cpu().numpy()[:, :(n + 7) // 8])
