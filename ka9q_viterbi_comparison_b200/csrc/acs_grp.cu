@@ -497,11 +497,36 @@ __device__ __forceinline__ int bm_post(int sum) {
     return sum;
 }
 
+// The symbols of one group of five steps in registers (K=9 kernels, GRP_SYM_PREFETCH): loaded one group AHEAD of the table
+// build that consumes them, so the build does not wait on global memory (ncu, ka9q29: 0.98 long-scoreboard stall cycles
+// per issue with the loads inside the build). An experiment that did not pay: see the kernel.
+template <int R, int SB> struct GroupSyms {
+    static constexpr int BYTES = NL * R * SB, WORDS = (BYTES + 3) / 4;
+    uint32_t w[WORDS];
+    __device__ __forceinline__ void load(const unsigned char* p, int valid_bytes) {
+#pragma unroll
+        for (int i = 0; i < WORDS; i++) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if (i * 4 + b < BYTES && i * 4 + b < valid_bytes) v |= (uint32_t)__ldg(p + i * 4 + b) << (8 * b);
+            w[i] = v;
+        }
+    }
+    template <int POLICY>
+    __device__ __forceinline__ int symbol(int s, int i) const {      // s, i compile-time after unrolling
+        const int b = (s * R + i) * SB;
+        const uint32_t v = (w[b >> 2] >> ((b & 3) * 8)) & (SB == 2 ? 0xffffu : 0xffu);
+        return (SB == 2) ? (int)(int16_t)v : (POLICY == P_WY_U8) ? (int)(int8_t)v : (int)v;
+    }
+};
+
 // Cooperative table build for TPF = 4 (K=9): per step, each of the frame's four threads evaluates NCW/4 code
 // words as subset sums of the per-symbol costs, fetches the lane-1 partner (code word ^ D_s) with one shuffle
 // and writes its NCW/4 entries. ~4x fewer instructions than one bm_eval per code word and task.
 template <int POLICY, class CODE, class CF, bool PUNCT>
-__device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl) {
+__device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl,
+                                                 const GroupSyms<CF::R, CF::SB>* gs = nullptr) {
     constexpr int R = CF::R, NPT = CF::NCW / 4, LOGN = (NPT == 1 ? 0 : NPT == 2 ? 1 : NPT == 4 ? 2 : NPT == 8 ? 3 : 4);
     static_assert(CF::TPF == 4 && CF::NCW >= 4 && (1 << LOGN) == NPT, "four threads per frame, NCW/4 code words each");
     const uint32_t buf = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
@@ -514,7 +539,7 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
         int v0[R], v1[R];
 #pragma unroll
         for (int i = 0; i < R; i++) {
-            const int sym = ld_step_symbol<POLICY, R, CF::SB, PUNCT>(a, sp, t, i);
+            const int sym = (!PUNCT && gs) ? gs->template symbol<POLICY>(s, i) : ld_step_symbol<POLICY, R, CF::SB, PUNCT>(a, sp, t, i);
             symbol_costs<POLICY>(sym, a, v0[i], v1[i]);
         }
         // code words of this thread: c = tx * NPT + j; the two top bits of c come from tx
@@ -545,10 +570,11 @@ __device__ __forceinline__ void fill_tables_coop(const GrpArgs& a, const unsigne
 // entry (s, c) = { pack(bm[c], bm[c ^ D_s]), pack(cm[c], cm[c ^ D_s]) }, D_s = code-word difference between the
 // two lanes of a register in phase s. One task computes bm of c and c ^ D_s once and writes both entries.
 template <int POLICY, class CODE, class CF, bool PUNCT>
-__device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl) {
+__device__ __forceinline__ void fill_tables(const GrpArgs& a, const unsigned char* sp, int g, uint32_t tab_addr, int tx, int fl,
+                                            const GroupSyms<CF::R, CF::SB>* gs = nullptr) {
     constexpr int R = CF::R, HALF = CF::NCW / 2;
     if constexpr (CF::TPF == 4 && CF::NCW >= 4) {
-        fill_tables_coop<POLICY, CODE, CF, PUNCT>(a, sp, g, tab_addr, tx, fl);
+        fill_tables_coop<POLICY, CODE, CF, PUNCT>(a, sp, g, tab_addr, tx, fl, gs);
         return;
     }
     const uint32_t buf = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
@@ -733,7 +759,21 @@ acs_grp_kernel(const GrpArgs a) {
     unsigned long long* drow = a.dec + ((size_t)a.step0 * a.n_frames + frame) * CF::TPF + tx;
 
     const int ngroups = (a.nsteps + NL - 1) / NL;
-    if (ngroups > 0) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, 0, tab_addr, tx, fl);
+    // Measured and left off: with the prefetch the K=9 kernels take 7-9 more registers (ka9q29 96 -> 103: one resident
+    // block fewer) and run SLOWER -- ka9q29 14.27 -> 15.08 ms, spiral29 18.83 -> 19.48, spiral49 27.78 -> 28.46, wy-u8 K9R4
+    // 30.17 -> 32.11 per 256 Ki frames; capping the registers (5 blocks) spills: 14.93 / 19.80 / 29.92 / 33.70.
+#ifndef GRP_SYM_PREFETCH
+#define GRP_SYM_PREFETCH 0
+#endif
+    constexpr bool PREFETCH = GRP_SYM_PREFETCH && CF::TPF == 4 && CF::NCW >= 4 && !PUNCT;
+    using GS = GroupSyms<CF::R, CF::SB>;
+    GS gs;                                   // symbols of the group whose tables are built next
+    auto load_group = [&](int g) {
+        if (PREFETCH && g < ngroups) gs.load(sp + (size_t)g * GS::BYTES, (a.nsteps - g * NL) * CF::R * CF::SB);
+    };
+    load_group(0);
+    if (ngroups > 0) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, 0, tab_addr, tx, fl, PREFETCH ? &gs : nullptr);
+    load_group(1);
     if (CF::TPF >= 32) __syncthreads(); else __syncwarp();
 
     // Whole groups run their five steps unconditionally: a step guarded by `if (nsub > s)` ends in a join where ptxas
@@ -758,7 +798,11 @@ acs_grp_kernel(const GrpArgs a) {
     const int nmain = UNCOND ? nfull : 0;
 #pragma unroll 1
     for (int g = 0; g < nmain; g++) {
-        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, g + 1, tab_addr, tx, fl);
+        {
+            const GS cur = gs;
+            load_group(g + 2);
+            if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, g + 1, tab_addr, tx, fl, PREFETCH ? &cur : nullptr);
+        }
         const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
         step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
         step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);
@@ -772,7 +816,11 @@ acs_grp_kernel(const GrpArgs a) {
 #pragma unroll 1
     for (int g = nmain; g < ngroups; g++) {
         const int nsub = min(NL, a.nsteps - g * NL);
-        if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, g + 1, tab_addr, tx, fl);
+        {
+            const GS cur = gs;
+            load_group(g + 2);
+            if (g + 1 < ngroups) fill_tables<POLICY, CODE, CF, PUNCT>(a, sp, g + 1, tab_addr, tx, fl, PREFETCH ? &cur : nullptr);
+        }
         const uint32_t gt = tab_addr + (uint32_t)(g & 1) * (NL * CF::SUBTAB);
         step<POLICY, CODE, CF, 0, false>(w, fs, a, gt, cx8[0], drow, live, met_addr, s_red, rpar, tid, tx);
         if (nsub > 1) step<POLICY, CODE, CF, 1, false>(w, fs, a, gt + CF::SUBTAB, cx8[1], drow + dstride, live, met_addr, s_red, rpar, tid, tx);

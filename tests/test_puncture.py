@@ -255,3 +255,52 @@ def test_pipelined_punctured_host_decode():
             qo, _ = q.decode(erased[f], nbits)
             assert np.array_equal(got[f], qo), f
             q.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["ka9q27", "wy_sse_u8_k9r2", "ka9q615"])
+def test_punctured_update_continues_across_calls(name):
+    """A pattern that covers half a frame, applied twice (ka9q / williamyang updates continue from the previous call's
+    position): equals one full-rate update of the expanded symbols."""
+    import torch
+    import ka9q_viterbi_comparison_b200 as kv
+    from test_gpu_parity import CASES
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    n_frames = 3 if K == 15 else 11
+    half = 60 if K == 15 else 132                       # steps per call
+    T = 2 * half
+    nbits = T - (K - 1)
+    lo, hi = o.soft_range(c)
+    fill = (lo + hi + 1) // 2
+    dt = o.sym_dtype(c)
+    sb = np.dtype(dt).itemsize
+    code = np.array([1, 0, 1, 1, 1, 0, 1], dtype=np.uint8)
+    rng = np.random.default_rng(4)
+    full = rng.integers(lo, hi + 1, (n_frames, T * R)).astype(dt)
+    keep = np.resize(code.astype(bool), half * R)        # the code index restarts in every call
+    tx = [np.ascontiguousarray(full[:, h * half * R:(h + 1) * half * R][:, keep]) for h in (0, 1)]
+    erased = full.copy()
+    for h in (0, 1):
+        part = erased[:, h * half * R:(h + 1) * half * R]
+        part[:, ~keep] = fill
+    with kv.BatchDecoder(codec, T, n_frames, K=K, R=R) as dec:
+        dec.reset()
+        dec.set_variant(2)
+        assert dec.set_puncturing([(code, half * R)], fill) == tx[0].shape[1]
+        for h in (0, 1):
+            d_tx = torch.from_numpy(tx[h].view(np.uint8).reshape(n_frames, -1).copy()).cuda()
+            dec.update_punctured_dev(d_tx, tx[h].shape[1] * sb)
+            dec.sync()
+        assert dec.steps_done == T
+        got = dec.chainback(nbits)
+        mets = [dec.metrics(f) for f in range(n_frames)]
+        dec.reset()
+        dec.update(erased)
+        assert np.array_equal(dec.chainback(nbits), got)
+    for f in (0, n_frames - 1):
+        q = o.Oracle(c, T)
+        qo, _ = q.decode(erased[f], nbits)
+        assert np.array_equal(got[f], qo), f
+        assert np.array_equal(mets[f], q.metrics()), f
+        q.close()

@@ -187,3 +187,40 @@ def test_stream_host_buffer_entries_match_the_device_entries():
         b.sync()
         assert nbits == n == depth
         assert np.array_equal(tail, d_out.cpu().numpy()[:, :(n + 7) // 8])
+
+
+@pytest.mark.parametrize("name", ["ka9q27", "spiral49", "ka9q615"])
+def test_short_stream_flushed_before_the_window_fills_equals_a_frame_decode(name):
+    """A tail-terminated stream shorter than the ring: no push emits anything, flush(endstate 0) emits every data bit and
+    must equal the ordinary init + update + chainback of the same symbols (and the data at low noise); reset and reuse."""
+    import torch
+    codec, K, R = CASES[name]
+    c = o.codec_by_name(name)
+    chunk, depth, n_streams = 16, 96, 4
+    npush = 5                                          # 80 steps < depth + chunk = 112
+    T = npush * chunk
+    nbits = T - (K - 1)
+    nbytes = (nbits + 7) // 8
+    for seed in (1, 2):                                # the second pass reuses the stream object after reset
+        frames = [o.make_frame(c, nbits // 8, 0.3, seed=seed, frame=f) for f in range(n_streams)]
+        # make_frame gives (nbits//8)*8 + K-1 steps: pad with "strong zero" symbols up to T steps (more tail)
+        lo, hi = o.soft_range(c)
+        zero_sym = lo
+        syms = np.full((n_streams, T * R), zero_sym, dtype=o.sym_dtype(c))
+        for f, (_, s) in enumerate(frames):
+            syms[f, :s.size] = s
+        if seed == 1:
+            sd = kv.StreamDecoder(codec, n_streams, depth, chunk, K=K, R=R)
+        sd.reset(0)
+        for p in range(npush):
+            assert sd.push(syms[:, p * chunk * R:(p + 1) * chunk * R]) is None
+        tail, n = sd.flush(endstate=0)
+        assert n == nbits and sd.emitted == nbits
+        with kv.BatchDecoder(codec, T, n_streams, K=K, R=R) as dec:
+            dec.reset()
+            dec.update(syms)
+            want = dec.chainback(nbits)
+        assert np.array_equal(tail[:, :nbytes], want[:, :nbytes])
+        for f, (d, _) in enumerate(frames):
+            assert np.array_equal(tail[f, :d.size], d), f
+    sd.close()
