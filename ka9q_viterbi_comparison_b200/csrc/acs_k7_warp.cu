@@ -51,6 +51,42 @@ __device__ __forceinline__ int branch_metric_rt(const CodecParams& c, unsigned c
     return (s >> 2) & 63;
 }
 
+// ---- latency helpers (round 2) ------------------------------------------------------------------------------------
+// r = 1/2 codes: the lane that fetched a step's symbols also evaluates the step's FOUR branch metrics (code words 0..3)
+// and packs them into one word (two for 16-bit metrics); a step then broadcasts that word and every lane picks its own
+// code word's field with a shift -- instead of broadcasting the symbols and evaluating the metric in all 32 lanes (~9
+// instructions per step off every lane's stream).
+#ifndef WARP_BM_PRE
+#define WARP_BM_PRE 1
+#endif
+template <int POLICY> struct BmPack {
+    static constexpr bool wide = (POLICY == P_WY_U16);
+    static constexpr int WORDS = wide ? 2 : 1;
+    __device__ __forceinline__ static void pack(const CodecParams& c, const int* sym, uint32_t* out) {
+        const uint32_t b0 = (uint32_t)branch_metric<POLICY>(c, 0u, sym), b1 = (uint32_t)branch_metric<POLICY>(c, 1u, sym);
+        const uint32_t b2 = (uint32_t)branch_metric<POLICY>(c, 2u, sym), b3 = (uint32_t)branch_metric<POLICY>(c, 3u, sym);
+        if (wide) { out[0] = b0 | (b1 << 16); out[1] = b2 | (b3 << 16); }
+        else out[0] = b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+    }
+    // field of code word cw out of the broadcast word(s)
+    __device__ __forceinline__ static int pick(const uint32_t* w, unsigned cw) {
+        if (wide) return (int)(((cw & 2u) ? w[1] : w[0]) >> ((cw & 1u) * 16) & 0xffffu);
+        return (int)((w[0] >> (cw * 8u)) & 0xffu);
+    }
+};
+// ka9q modular policy on UNWRAPPED metrics (reference metric = U mod 256): the candidate difference stays below 128
+// (bound: acs_k7.cu header; K=9: the CPU suite), so the reference's (int8)(m0 - m1) > 0 is the plain compare and the
+// mod-256 masking leaves the dependent chain: add -> min instead of add -> and -> sub -> sign-extend -> compare -> select.
+__device__ __forceinline__ void acs_mod_unwrapped(int lo, int hi, int bm, int& s0, int& s1, int& d0, int& d1) {
+    const int cm = 15 - bm;
+    const int m0 = lo + bm, m1 = hi + cm, m2 = lo + cm, m3 = hi + bm;
+    d0 = m0 > m1; d1 = m2 > m3;
+    s0 = min(m0, m1); s1 = min(m2, m3);
+}
+#ifndef WARP_MOD_UNWRAPPED
+#define WARP_MOD_UNWRAPPED 1
+#endif
+
 // RT = code rate known at compile time (2, 3, 4) or 0: run-time c.R (up to MAX_R).
 // Latency matters here as much as throughput -- this is the family a single frame through the reference's
 // create/init/update/chainback API runs on (src/main.cpp:264-278) -- so nothing in the step loop waits on global
@@ -70,6 +106,14 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
     uint16_t* gm = a.metrics + (size_t)frame * 64;
     int lo = gm[lane], hi = gm[lane + 32];
     if (PolicyTraits<POLICY>::is_signed16) { lo = (int16_t)lo; hi = (int16_t)hi; }
+    constexpr bool UNWRAP = WARP_MOD_UNWRAPPED && POLICY == P_KA9Q_U8_MOD;
+    constexpr bool PRE = WARP_BM_PRE && RT == 2;
+    constexpr int CW = PRE ? BmPack<POLICY>::WORDS : WPS;          // words a step broadcasts
+    if (UNWRAP) {      // around state 0 (lane 0's lo): U = 256 + m0 + (int8)(m - m0)
+        const int m0 = __shfl_sync(0xffffffffu, lo, 0);
+        lo = 256 + m0 + (int)(int8_t)(lo - m0);
+        hi = 256 + m0 + (int)(int8_t)(hi - m0);
+    }
     const unsigned cw = a.cw[lane];                                // code word of butterfly `lane` (host table)
     const unsigned char* sp = (const unsigned char*)a.syms + (size_t)frame * a.sym_stride;
     unsigned long long rsum = 0;     // minima subtracted by this launch's renormalisations (uniform over the warp)
@@ -77,39 +121,64 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
     const int src0 = lane >> 1, src1 = 16 + (lane >> 1);
     const bool odd = lane & 1;
 
+    auto symbols_of = [&](const uint32_t* sw, int* sym) {
+#pragma unroll
+        for (int r = 0; r < (RT ? RT : MAX_R); r++) {
+            if (r < R) {
+                const int bpos = r * SYMB;
+                const uint32_t v = sw[bpos >> 2] >> ((bpos & 3) * 8);
+                sym[r] = (POLICY == P_WY_U16) ? (int)(int16_t)(v & 0xffffu)
+                       : (POLICY == P_WY_U8) ? (int)(int8_t)(v & 0xffu) : (int)(v & 0xffu);
+            }
+        }
+    };
     auto fetch = [&](uint32_t (&buf)[WPS], int t0) {              // this lane's step of the 32 starting at t0
         const int t = t0 + lane;
+        uint32_t raw[WPS];
 #pragma unroll
-        for (int w = 0; w < WPS; w++) buf[w] = 0;
+        for (int w = 0; w < WPS; w++) raw[w] = 0;
         if (t < a.nsteps) {
             const unsigned char* p = sp + (size_t)t * step_bytes;
 #pragma unroll
             for (int j = 0; j < WPS * 4; j++)
-                if (j < step_bytes) buf[j >> 2] |= (uint32_t)__ldg(p + j) << ((j & 3) * 8);
+                if (j < step_bytes) raw[j >> 2] |= (uint32_t)__ldg(p + j) << ((j & 3) * 8);
+        }
+#pragma unroll
+        for (int w = 0; w < WPS; w++) buf[w] = raw[w];
+    };
+    // raw symbol words of the lane's step -> the words a step broadcasts. Called when a block of 32 steps is ENTERED, a
+    // whole block after the loads were issued: evaluating the metrics right behind the loads would expose the global
+    // round trip every 32 steps (measured: wy-u8 K9R2 single frame 638 -> 759 us that way).
+    auto prepare = [&](const uint32_t (&raw)[WPS], uint32_t (&out)[CW]) {
+        if constexpr (PRE) {
+            int sym[RT ? RT : MAX_R];
+            symbols_of(raw, sym);
+            BmPack<POLICY>::pack(c, sym, out);
+        } else {
+#pragma unroll
+            for (int w = 0; w < WPS; w++) out[w] = raw[w];
         }
     };
-    uint32_t cur[WPS], nxt[WPS];
-    fetch(cur, 0);
+    uint32_t cur[CW], nxt[WPS];
+    fetch(nxt, 0);
     for (int t0 = 0; t0 < a.nsteps; t0 += 32) {
+        prepare(nxt, cur);
         fetch(nxt, t0 + 32);
         const int nhere = min(32, a.nsteps - t0);
         for (int i = 0; i < nhere; i++) {
-            uint32_t sw[WPS];
+            uint32_t sw[CW];
 #pragma unroll
-            for (int w = 0; w < WPS; w++) sw[w] = __shfl_sync(0xffffffffu, cur[w], i);
-            int sym[RT ? RT : MAX_R];
-#pragma unroll
-            for (int r = 0; r < (RT ? RT : MAX_R); r++) {
-                if (r < R) {
-                    const int bpos = r * SYMB;
-                    const uint32_t v = sw[bpos >> 2] >> ((bpos & 3) * 8);
-                    sym[r] = (POLICY == P_WY_U16) ? (int)(int16_t)(v & 0xffffu)
-                           : (POLICY == P_WY_U8) ? (int)(int8_t)(v & 0xffu) : (int)(v & 0xffu);
-                }
+            for (int w = 0; w < CW; w++) sw[w] = __shfl_sync(0xffffffffu, cur[w], i);
+            int bm;
+            if constexpr (PRE) bm = BmPack<POLICY>::pick(sw, cw);
+            else {
+                int sym[RT ? RT : MAX_R];
+                symbols_of(sw, sym);
+                bm = branch_metric_rt<POLICY, RT>(c, cw, sym);
             }
-            const int bm = branch_metric_rt<POLICY, RT>(c, cw, sym);
             int v0, v1, d0, d1;
-            acs<POLICY>(c.max_error, lo, hi, bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
+            if constexpr (UNWRAP) acs_mod_unwrapped(lo, hi, bm, v0, v1, d0, d1);
+            else acs<POLICY>(c.max_error, lo, hi, bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
             const unsigned w0 = __ballot_sync(0xffffffffu, d0), w1 = __ballot_sync(0xffffffffu, d1);
             const int a0 = __shfl_sync(0xffffffffu, v0, src0), a1 = __shfl_sync(0xffffffffu, v1, src0);
             const int c0 = __shfl_sync(0xffffffffu, v0, src1), c1 = __shfl_sync(0xffffffffu, v1, src1);
@@ -126,10 +195,9 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
                 }
             }
         }
-#pragma unroll
-        for (int w = 0; w < WPS; w++) cur[w] = nxt[w];
     }
     if (lane == 0 && a.err && rsum) a.err[frame] += rsum;
+    if (UNWRAP) { lo &= 255; hi &= 255; }
     gm[lane] = (uint16_t)lo;
     gm[lane + 32] = (uint16_t)hi;
 }
@@ -159,48 +227,87 @@ __global__ void __launch_bounds__(128) acs_k9_warp_kernel(const GenericArgs a) {
     for (int i = 0; i < NS; i++) m[i] = gm[lane + 32 * i];
 #pragma unroll
     for (int b = 0; b < NBF; b++) cw[b] = a.cw[lane + 32 * b];
+    constexpr bool UNWRAP = WARP_MOD_UNWRAPPED && POLICY == P_KA9Q_U8_MOD;
+    // (the williamyang policies measured slower with the packed metrics here -- wy-u8 K9R2 single frame 638 -> 759 us in
+    // the same run -- while ka9q29 / spiral29 gained 27 % / 20 %: four butterflies per lane share one symbol decode)
+    constexpr bool PRE = WARP_BM_PRE && RT == 2 && !PolicyTraits<POLICY>::is_wy;
+    constexpr int CW = PRE ? BmPack<POLICY>::WORDS : WPS;          // words a step broadcasts
+    if (UNWRAP) {      // around state 0 (lane 0, slot 0): U = 256 + m0 + (int8)(m - m0)
+        const int m0 = __shfl_sync(0xffffffffu, m[0], 0);
+#pragma unroll
+        for (int i = 0; i < NS; i++) m[i] = 256 + m0 + (int)(int8_t)(m[i] - m0);
+    }
     const unsigned char* sp = (const unsigned char*)a.syms + (size_t)frame * a.sym_stride;
     unsigned long long rsum = 0;     // minima subtracted by this launch's renormalisations (uniform over the warp)
     uint32_t* drow = a.dec + ((size_t)frame * a.dec_rows + a.step0) * 8;
     const int srcA = lane >> 1, srcB = 16 + (lane >> 1);
     const bool odd = lane & 1;
 
+    auto symbols_of = [&](const uint32_t* sw, int* sym) {
+#pragma unroll
+        for (int r = 0; r < (RT ? RT : MAX_R); r++) {
+            if (r < R) {
+                const int bpos = r * SYMB;
+                const uint32_t v = sw[bpos >> 2] >> ((bpos & 3) * 8);
+                sym[r] = (POLICY == P_WY_U16) ? (int)(int16_t)(v & 0xffffu)
+                       : (POLICY == P_WY_U8) ? (int)(int8_t)(v & 0xffu) : (int)(v & 0xffu);
+            }
+        }
+    };
     auto fetch = [&](uint32_t (&buf)[WPS], int t0) {
         const int t = t0 + lane;
+        uint32_t raw[WPS];
 #pragma unroll
-        for (int w = 0; w < WPS; w++) buf[w] = 0;
+        for (int w = 0; w < WPS; w++) raw[w] = 0;
         if (t < a.nsteps) {
             const unsigned char* p = sp + (size_t)t * step_bytes;
 #pragma unroll
             for (int j = 0; j < WPS * 4; j++)
-                if (j < step_bytes) buf[j >> 2] |= (uint32_t)__ldg(p + j) << ((j & 3) * 8);
+                if (j < step_bytes) raw[j >> 2] |= (uint32_t)__ldg(p + j) << ((j & 3) * 8);
+        }
+#pragma unroll
+        for (int w = 0; w < WPS; w++) buf[w] = raw[w];
+    };
+    // raw symbol words of the lane's step -> the words a step broadcasts. Called when a block of 32 steps is ENTERED, a
+    // whole block after the loads were issued: evaluating the metrics right behind the loads would expose the global
+    // round trip every 32 steps (measured: wy-u8 K9R2 single frame 638 -> 759 us that way).
+    auto prepare = [&](const uint32_t (&raw)[WPS], uint32_t (&out)[CW]) {
+        if constexpr (PRE) {
+            int sym[RT ? RT : MAX_R];
+            symbols_of(raw, sym);
+            BmPack<POLICY>::pack(c, sym, out);
+        } else {
+#pragma unroll
+            for (int w = 0; w < WPS; w++) out[w] = raw[w];
         }
     };
-    uint32_t cur[WPS], nxt[WPS];
-    fetch(cur, 0);
+    uint32_t cur[CW], nxt[WPS];
+    fetch(nxt, 0);
     for (int t0 = 0; t0 < a.nsteps; t0 += 32) {
+        prepare(nxt, cur);
         fetch(nxt, t0 + 32);
         const int nhere = min(32, a.nsteps - t0);
+        if (UNWRAP) {      // survivors travel as 16-bit halves: bring the unwrapped values down by a multiple of 256
+            const int ref = __shfl_sync(0xffffffffu, m[0], 0);
+            const int sub = ref >= 512 ? ((ref - 256) & ~255) : 0;
+#pragma unroll
+            for (int s = 0; s < NS; s++) m[s] -= sub;
+        }
         for (int i = 0; i < nhere; i++) {
-            uint32_t sw[WPS];
+            uint32_t sw[CW];
 #pragma unroll
-            for (int w = 0; w < WPS; w++) sw[w] = __shfl_sync(0xffffffffu, cur[w], i);
+            for (int w = 0; w < CW; w++) sw[w] = __shfl_sync(0xffffffffu, cur[w], i);
             int sym[RT ? RT : MAX_R];
-#pragma unroll
-            for (int r = 0; r < (RT ? RT : MAX_R); r++) {
-                if (r < R) {
-                    const int bpos = r * SYMB;
-                    const uint32_t v = sw[bpos >> 2] >> ((bpos & 3) * 8);
-                    sym[r] = (POLICY == P_WY_U16) ? (int)(int16_t)(v & 0xffffu)
-                           : (POLICY == P_WY_U8) ? (int)(int8_t)(v & 0xffu) : (int)(v & 0xffu);
-                }
-            }
+            if constexpr (!PRE) symbols_of(sw, sym);
             uint32_t pk[NBF], row[2 * NBF];
 #pragma unroll
             for (int b = 0; b < NBF; b++) {
-                const int bm = branch_metric_rt<POLICY, RT>(c, cw[b], sym);
+                int bm;
+                if constexpr (PRE) bm = BmPack<POLICY>::pick(sw, cw[b]);
+                else bm = branch_metric_rt<POLICY, RT>(c, cw[b], sym);
                 int v0, v1, d0, d1;
-                acs<POLICY>(c.max_error, m[b], m[b + NBF], bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
+                if constexpr (UNWRAP) acs_mod_unwrapped(m[b], m[b + NBF], bm, v0, v1, d0, d1);
+                else acs<POLICY>(c.max_error, m[b], m[b + NBF], bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
                 row[2 * b] = __ballot_sync(0xffffffffu, d0);
                 row[2 * b + 1] = __ballot_sync(0xffffffffu, d1);
                 pk[b] = ((uint32_t)v0 & 0xffffu) | ((uint32_t)v1 << 16);
@@ -228,12 +335,10 @@ __global__ void __launch_bounds__(128) acs_k9_warp_kernel(const GenericArgs a) {
                 }
             }
         }
-#pragma unroll
-        for (int w = 0; w < WPS; w++) cur[w] = nxt[w];
     }
     if (lane == 0 && a.err && rsum) a.err[frame] += rsum;
 #pragma unroll
-    for (int i = 0; i < NS; i++) gm[lane + 32 * i] = (uint16_t)m[i];
+    for (int i = 0; i < NS; i++) gm[lane + 32 * i] = (uint16_t)(UNWRAP ? (m[i] & 255) : m[i]);
 }
 
 template <int POLICY>
