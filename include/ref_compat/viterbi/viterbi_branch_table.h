@@ -2,7 +2,7 @@
  * a decoder (williamyang_viterbi_lib/include/viterbi/viterbi_branch_table.h:19-55; src/main.cpp:163), on top of the
  * C-ABI of b200_viterbi.h: it only records the generator polynomials and the two soft-decision levels; the per-state
  * code-word table itself is built on the device side by b200v_batch_create. Put include/ref_compat/ BEFORE the
- * reference's include directory and src/main.cpp's twelve williamyang rows run on the CUDA path unmodified. */
+ * reference's include directory and src/main.cpp's williamyang rows run on the CUDA path unmodified. */
 #pragma once
 #include <stddef.h>
 #include <stdint.h>

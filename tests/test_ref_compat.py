@@ -2,7 +2,7 @@
 CPU: the library exports every symbol include/ref_compat/b200_ref_compat.h declares. GPU: the reference's own
 benchmark driver (src/main.cpp, unmodified, compiled by `make -C oracle compat_main` against include/ref_compat/)
 runs all six codecs through the CUDA path and decodes its noiseless frames without bit errors -- the nine ka9q / spiral
-rows through the per-codec functions, the twelve williamyang rows (sse_u8, avx_u8, sse_u16, avx_u16 x three codes) through
+rows through the per-codec functions, the 24 williamyang rows (sse_u8, avx_u8, sse_u16, avx_u16 x six codes) through
 include/ref_compat/viterbi/, the header-compatible ViterbiDecoder_Core over the C-ABI."""
 import json
 import os
@@ -60,7 +60,7 @@ def test_reference_main_runs_on_the_cuda_path(tmp_path):
     # main_b200 was compiled with include/ref_compat/ first, so they are the CUDA-backed classes (the binary does not
     # contain the reference's SIMD decoders: nm shows no _mm-based update, and the rows decode without errors)
     ours = [r for r in rows if r["name"] in ("sse_u8", "avx_u8", "sse_u16", "avx_u16")]
-    assert len(ours) == len(rows) - 9 and len(ours) >= 12, [(r["name"], r["K"], r["R"]) for r in rows]
+    assert len(ours) == len(rows) - 9 and len(ours) == 24, [(r["name"], r["K"], r["R"]) for r in rows]
     for r in ours:
         assert r["total_samples"] >= 2
         assert r["total_bit_errors"] == 0, (r["name"], r["K"], r["R"], r["bit_error_rate"])
