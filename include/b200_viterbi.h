@@ -97,7 +97,7 @@ int b200v_batch_set_stream(b200v_batch* h, void* cuda_stream);
 /* Choose the kernel family: 0 = automatic (fastest available for the codec/polynomials),
  * 1 = generic shared-memory kernel (any K<=16, any polynomial), 2 = register-resident specialised kernel,
  * 3 = warp-per-frame shuffle/ballot kernel (any K=7 or K=9 code and policy; the automatic family for small batches
- *     (K=7: up to 2048 frames, K=9: up to 1024) and for polynomial sets without a family-2 instance, and the
+ *     (K=7: up to 4096 frames, K=9: up to 2048) and for polynomial sets without a family-2 instance, and the
  *     measured alternative to family 2).
  * Returns B200V_ERR_ARG if the requested family does not exist for this instance. */
 int b200v_batch_set_variant(b200v_batch* h, int variant);

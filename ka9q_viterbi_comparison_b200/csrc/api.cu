@@ -211,8 +211,11 @@ static int create_impl(b200v_batch* h, int starting_state);
 // latency-bound: a frame that owns a warp advances a step in ~70 ns against ~200 ns for a frame that owns one thread
 // of the register kernel (measured, 8198-step frames: 1 frame 0.58 vs 1.63 ms, 1024 frames 2.7 vs 3.6 ms including
 // the upload, equal at 4096 frames), so up to 2048 frames the warp-per-frame family is the automatic choice.
-constexpr int K7_WARP_MAX_FRAMES = 2048;
-constexpr int K9_WARP_MAX_FRAMES = 1024;   // K=9 (8 states per lane): single frame 1.06-1.55 -> 0.66-0.94 ms, still ahead at 1024 frames
+// Round 2 (faster warp-per-frame step, r = 1/2 codes): update + chainback through the host-buffer calls, 8198- / 4104-step
+// frames, warp-per-frame against the register / group family: K=7 4096 frames 9.97 vs 11.54 ms (8192: 20.4 vs 19.8),
+// K=9 2048 frames 3.57 vs 3.76 ms (4096: 6.44 vs 6.35) -> the limits move from 2048 / 1024 to 4096 / 2048 frames.
+constexpr int K7_WARP_MAX_FRAMES = 4096;
+constexpr int K9_WARP_MAX_FRAMES = 2048;   // K=9 (8 states per lane)
 static int fallback_variant(const b200v_batch* h) {
     if (k7_warp_supported(h->c) &&
         (!h->has_fast || h->n_frames <= (h->c.K == 7 ? K7_WARP_MAX_FRAMES : K9_WARP_MAX_FRAMES))) return 3;

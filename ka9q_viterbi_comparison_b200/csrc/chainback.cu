@@ -185,8 +185,11 @@ static bool par_geometry(const ChainbackArgs& a, unsigned& L, unsigned& D, unsig
     // 16384-bit frames, K=15 x 2048 frames 12.3 -> 1.9 ms, K=9 x 4096 frames 9.4 -> 2.6 ms.
     // The K=7 register layout keeps its per-frame kernel there: it streams whole rows, coalesced (4096 frames x
     // 16384 bits: 2.17 ms against 2.36 ms block-parallel).
+    // Round 2, K=7 register layout re-measured by frame count (device time of the traceback, per-frame / block-parallel):
+    // 2048 x 65536 bits 10.06 / 4.13 ms, 4096 x 16384 2.50 / 2.33, 8192 x 16384 2.34 / 3.67: the streaming kernel needs
+    // thousands of frames in flight, so it takes over above 4096 frames only.
     if (!forced && (unsigned long long)a.count * a.nbits > (1ull << 24)) {
-        if (a.layout == DL_K7_INTERLEAVED) return false;
+        if (a.layout == DL_K7_INTERLEAVED && a.count > 4096) return false;
         L = max(L, D);
     }
     B = (a.nbits + L - 1) / L;

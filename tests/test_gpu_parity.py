@@ -424,9 +424,9 @@ def test_wy_u16_out_of_range_symbols_take_the_generic_family(name):
     T = 90 if K == 15 else 300
     nbits = T - (K - 1)
     rng = np.random.default_rng(16)
-    # K=7 / K=9: batches of up to 2048 / 1024 frames run on the warp-per-frame family anyway (exact for any input), so the
+    # K=7 / K=9: batches of up to 4096 / 2048 frames run on the warp-per-frame family anyway (exact for any input), so the
     # routing away from the register kernel needs a larger batch; frames 3.. repeat the first three
-    n_frames = 2051 if K == 7 else 1027 if K == 9 else 3
+    n_frames = 4099 if K == 7 else 2051 if K == 9 else 3
     in_range = np.resize(rng.integers(-127, 128, size=(3, T * R)), (n_frames, T * R)).astype(np.int16)
     wild = rng.integers(-32768, 32768, size=(3, T * R)).astype(np.int16)
     wild[1, ::7] = -32768

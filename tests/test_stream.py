@@ -120,12 +120,12 @@ def test_stream_window_matches_the_oracle_window(name, terminated):
 
 
 def test_stream_many_streams_register_kernel():
-    """4096 streams: the K=7 register kernel (decision words interleaved across streams) writes the ring; the emitted
+    """4608 streams: the K=7 register kernel (decision words interleaved across streams) writes the ring; the emitted
     bits equal a whole-frame decode of the same symbols wherever the window is deep enough -- at low noise everywhere."""
     import torch
     codec, K, R = kv.KA9Q27, 7, 2
     c = o.codec_by_name("ka9q27")
-    n_streams, chunk, depth = 4096, 64, 64
+    n_streams, chunk, depth = 4608, 64, 64
     W = depth + chunk
     nbytes = 126
     nbits = nbytes * 8
