@@ -319,3 +319,36 @@ def test_oracle_matches_reference_on_common_codes(kr, K, R, poly, decoders):
             if sigma == 0.0:
                 assert np.array_equal(ro, data)
             r.close(); q.close()
+
+
+@pytest.mark.parametrize("name", ["ka9q27", "spiral49", "wy_sse_u16_k9r2", "ka9q615"])
+def test_window_walk_of_the_stream_tests_equals_the_oracle_chainback(name):
+    """tests/test_stream.py checks the sliding-window decoder against `walk` (a traceback through the oracle's canonical
+    decision vectors from a given state). Pin that helper: over a whole terminated frame, from end state 0, it must
+    reproduce the oracle's own chainback (which is pinned against the compiled reference above) -- with and without the
+    K-1 newest bits read from the state -- and a window in the middle must equal the same bits of the full traceback."""
+    import importlib
+    ts = importlib.import_module("test_stream")
+    c = o.codec_by_name(name)
+    K = c.K
+    nbytes = 12 if K == 15 else 40
+    nbits = nbytes * 8
+    T = nbits + K - 1
+    data, syms = o.make_frame(c, nbytes, 0.4, seed=9, frame=1)
+    q = o.Oracle(c, T)
+    want, rows = q.decode(syms, nbits)
+    q.close()
+    got = ts.walk(rows, K, 0, T - 1, 0, nbits, False)
+    assert np.array_equal(got, want)
+    # the newest K-1 bits of a walk that starts at state s are s itself: here the tail (zeros)
+    full = ts.walk(rows, K, 0, T - 1, 0, T, True)
+    assert np.array_equal(np.unpackbits(full)[:nbits], np.unpackbits(want)[:nbits])
+    assert not np.unpackbits(full)[nbits:T].any()
+    # a window: bits [16, 48) traced from the true state after row 79 (the K-1 newest input bits up to step 79)
+    bits = np.unpackbits(want)
+    top = 79
+    state = 0
+    for j in range(K - 1):
+        state |= int(bits[top - j]) << j
+    win = ts.walk(rows, K, state, top, 16, 32, False)
+    assert np.array_equal(np.unpackbits(win)[:32], bits[16:48])
