@@ -294,6 +294,13 @@ typedef struct b200v_sharded b200v_sharded;
 /* One b200v_batch per entry of devices[] (a device may appear more than once), sized for its shard. */
 b200v_sharded* b200v_sharded_create(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
                                     const int* devices, int n_devices, const b200v_wy_config* wy_config);
+/* The same with shards proportional to weights[] -- e.g. the host-to-device rate each GPU's link sustains when all copy at
+ * once (tools/h2d_probe.py: on an 8-GPU box four links gave 20 GB/s and four 35 GB/s; the end-to-end rate of equal shards is
+ * set by the slowest). b200v_shard_range_weighted gives the ranges: contiguous, every frame once. */
+int b200v_shard_range_weighted(int n_frames, const double* weights, int n_shards, int shard, int* frame0, int* count);
+b200v_sharded* b200v_sharded_create_weighted(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
+                                             const int* devices, const double* weights, int n_devices,
+                                             const b200v_wy_config* wy_config);
 void b200v_sharded_destroy(b200v_sharded* s);
 int b200v_sharded_num_shards(const b200v_sharded* s);
 int b200v_sharded_shard(const b200v_sharded* s, int shard, int* frame0, int* count);

@@ -6,6 +6,6 @@ this package only builds/loads it and mirrors the reference's decoder interface 
 from .decoder import (  # noqa: F401
     B200ViterbiError, BatchDecoder, WyConfig, CODEC_BY_NAME, STANDARD_POLYS, EXPORTED_SYMBOLS,
     KA9Q27, KA9Q29, KA9Q615, KA9Q224, SPIRAL27, SPIRAL29, SPIRAL47, SPIRAL49, SPIRAL615, WY_U8, WY_U16,
-    load_library, library_path, symbol_dtype, metric_dtype, shard_range, ShardedDecoder, decode_noalloc_dev, NOALLOC_SCRATCH_BYTES, StreamDecoder, PunctureSegment,
+    load_library, library_path, symbol_dtype, metric_dtype, shard_range, shard_range_weighted, ShardedDecoder, decode_noalloc_dev, NOALLOC_SCRATCH_BYTES, StreamDecoder, PunctureSegment,
 )
 from .build import build_library  # noqa: F401

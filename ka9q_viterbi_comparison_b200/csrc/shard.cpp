@@ -20,6 +20,25 @@ extern "C" int b200v_shard_range(int n_frames, int n_shards, int shard, int* fra
     return B200V_OK;
 }
 
+// Shards proportional to weights (e.g. the host-to-device rate each GPU's link sustains when all of them copy at once,
+// tools/h2d_probe.py): boundary g = round(B * prefix_weight(g) / total_weight), so the ranges are contiguous, cover every
+// frame once and depend only on the weights. Equal weights give b200v_shard_range's ranges up to rounding.
+extern "C" int b200v_shard_range_weighted(int n_frames, const double* weights, int n_shards, int shard, int* frame0, int* count) {
+    if (n_frames < 0 || n_shards <= 0 || shard < 0 || shard >= n_shards || !frame0 || !count || !weights) return B200V_ERR_ARG;
+    double total = 0, before = 0;
+    for (int g = 0; g < n_shards; g++) {
+        if (!(weights[g] >= 0)) return B200V_ERR_ARG;       // negative or NaN
+        total += weights[g];
+        if (g < shard) before += weights[g];
+    }
+    if (!(total > 0)) return B200V_ERR_ARG;
+    const long long lo = shard == 0 ? 0 : (long long)((double)n_frames * before / total + 0.5);
+    const long long hi = shard == n_shards - 1 ? n_frames : (long long)((double)n_frames * (before + weights[shard]) / total + 0.5);
+    *frame0 = (int)lo;
+    *count = (int)(hi > lo ? hi - lo : 0);
+    return B200V_OK;
+}
+
 struct b200v_sharded {
     int n_frames = 0, frame_steps = 0, sym_row = 0;
     std::vector<b200v_batch*> inst;
@@ -29,13 +48,25 @@ struct b200v_sharded {
 
 extern "C" b200v_sharded* b200v_sharded_create(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
                                                const int* devices, int n_devices, const b200v_wy_config* wy_config) {
+    return b200v_sharded_create_weighted(codec, K, R, poly, frame_steps, n_frames, devices, nullptr, n_devices, wy_config);
+}
+
+extern "C" b200v_sharded* b200v_sharded_create_weighted(int codec, int K, int R, const int* poly, int frame_steps, int n_frames,
+                                                        const int* devices, const double* weights, int n_devices,
+                                                        const b200v_wy_config* wy_config) {
     if (!devices || n_devices <= 0 || n_frames <= 0) return nullptr;
     b200v_sharded* s = new (std::nothrow) b200v_sharded();
     if (!s) return nullptr;
     s->n_frames = n_frames; s->frame_steps = frame_steps;
     for (int g = 0; g < n_devices; g++) {
         int f0 = 0, cnt = 0;
-        b200v_shard_range(n_frames, n_devices, g, &f0, &cnt);
+        const int rc = weights ? b200v_shard_range_weighted(n_frames, weights, n_devices, g, &f0, &cnt)
+                               : b200v_shard_range(n_frames, n_devices, g, &f0, &cnt);
+        if (rc != B200V_OK) {
+            for (b200v_batch* p : s->inst) b200v_batch_destroy(p);
+            delete s;
+            return nullptr;
+        }
         b200v_batch* h = cnt > 0 ? b200v_batch_create(codec, K, R, poly, frame_steps, cnt, devices[g], wy_config) : nullptr;
         if (cnt > 0 && !h) {
             for (b200v_batch* p : s->inst) b200v_batch_destroy(p);

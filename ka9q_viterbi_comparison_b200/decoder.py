@@ -120,6 +120,9 @@ def load_library():
         "b200v_batch_decode_punctured": (i32, [vp, vp, vp, u32]),
         "b200v_shard_range": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
         "b200v_sharded_create": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(WyConfig)]),
+        "b200v_shard_range_weighted": (i32, [i32, C.POINTER(C.c_double), i32, i32, C.POINTER(i32), C.POINTER(i32)]),
+        "b200v_sharded_create_weighted": (vp, [i32, i32, i32, C.POINTER(i32), i32, i32, C.POINTER(i32), C.POINTER(C.c_double), i32,
+                                               C.POINTER(WyConfig)]),
         "b200v_sharded_destroy": (None, [vp]),
         "b200v_sharded_num_shards": (i32, [vp]),
         "b200v_sharded_shard": (i32, [vp, i32, C.POINTER(i32), C.POINTER(i32)]),
@@ -152,7 +155,7 @@ EXPORTED_SYMBOLS = [
     "b200v_stream_steps", "b200v_stream_emitted", "b200v_stream_sync", "b200v_stream_batch", "b200v_batch_get_decisions",
     "b200v_batch_get_metrics", "b200v_batch_steps_done", "b200v_batch_accumulated_error", "b200v_batch_last_kernel_ms",
     "b200v_batch_launch_count", "b200v_batch_generate_dev", "b200v_batch_depuncture_dev", "b200v_batch_set_puncturing", "b200v_batch_update_punctured_dev",
-    "b200v_batch_decode_punctured_dev", "b200v_batch_decode_punctured", "b200v_shard_range", "b200v_sharded_create",
+    "b200v_batch_decode_punctured_dev", "b200v_batch_decode_punctured", "b200v_shard_range", "b200v_shard_range_weighted", "b200v_sharded_create", "b200v_sharded_create_weighted",
     "b200v_sharded_destroy", "b200v_sharded_num_shards", "b200v_sharded_shard", "b200v_sharded_decode",
     "b200v_sharded_last_error", "b200v_bind_host_to_device", "b200v_device_alloc", "b200v_device_free",
     "b200v_host_alloc_pinned", "b200v_host_free_pinned", "b200v_host_is_pinned", "b200v_memcpy_h2d", "b200v_memcpy_d2h",
@@ -478,11 +481,21 @@ def shard_range(n_frames, n_shards, shard):
     return f0.value, cnt.value
 
 
+def shard_range_weighted(n_frames, weights, shard):
+    """Contiguous frame range of shard `shard` when shards are proportional to `weights`."""
+    w = (C.c_double * len(weights))(*[float(x) for x in weights])
+    f0, cnt = C.c_int(), C.c_int()
+    rc = load_library().b200v_shard_range_weighted(n_frames, w, len(weights), shard, C.byref(f0), C.byref(cnt))
+    if rc != 0:
+        raise ValueError(f"bad weighted shard arguments ({n_frames}, {list(weights)}, {shard})")
+    return f0.value, cnt.value
+
+
 class ShardedDecoder:
     """One batch instance per device inside this process (b200v_sharded_*): frames are cut into contiguous
     ranges, each decoded on its device by its own host thread; no collective."""
 
-    def __init__(self, codec, frame_steps, n_frames, devices, K=0, R=0, poly=None):
+    def __init__(self, codec, frame_steps, n_frames, devices, K=0, R=0, poly=None, weights=None):
         self.lib = load_library()
         if isinstance(codec, str):
             codec = CODEC_BY_NAME[codec]
@@ -493,8 +506,13 @@ class ShardedDecoder:
         self.codec, self.n_frames, self.frame_steps = codec, n_frames, frame_steps
         self.sym_dtype = symbol_dtype(codec)
         devs = (C.c_int * len(devices))(*devices)
-        self.h = self.lib.b200v_sharded_create(codec, self.K, self.R, (C.c_int * len(poly))(*poly), frame_steps,
-                                               n_frames, devs, len(devices), None)
+        if weights is not None:
+            w = (C.c_double * len(devices))(*[float(x) for x in weights])
+            self.h = self.lib.b200v_sharded_create_weighted(codec, self.K, self.R, (C.c_int * len(poly))(*poly), frame_steps,
+                                                            n_frames, devs, w, len(devices), None)
+        else:
+            self.h = self.lib.b200v_sharded_create(codec, self.K, self.R, (C.c_int * len(poly))(*poly), frame_steps,
+                                                   n_frames, devs, len(devices), None)
         if not self.h:
             raise B200ViterbiError(f"b200v_sharded_create failed: {self.lib.b200v_last_error().decode()}")
 

@@ -97,3 +97,44 @@ def test_sharded_decode_matches_single_instance(name, codec):
         qo, _ = q.decode(syms[f], nbits)
         assert np.array_equal(out[f], qo)
         q.close()
+
+
+def test_weighted_shard_ranges_partition_the_batch():
+    """b200v_shard_range_weighted: contiguous, every frame exactly once, proportional to the weights; equal weights agree
+    with b200v_shard_range up to one frame; bad weights are rejected."""
+    for n_frames, weights in ((1000, [20.4] * 4 + [35.2] * 4), (7, [1, 1, 1]), (1 << 20, [1, 3]), (5, [0, 1, 0, 2]), (3, [5.0])):
+        pos, sizes = 0, []
+        for g in range(len(weights)):
+            f0, cnt = kv.shard_range_weighted(n_frames, weights, g)
+            assert f0 == pos and cnt >= 0
+            pos += cnt
+            sizes.append(cnt)
+        assert pos == n_frames
+        tot = float(sum(weights))
+        for g, w in enumerate(weights):
+            assert abs(sizes[g] - n_frames * w / tot) <= 1.0, (n_frames, weights, sizes)
+    for g in range(3):
+        a, b = kv.shard_range_weighted(301, [2, 2, 2], g), kv.shard_range(301, 3, g)
+        assert abs(a[0] - b[0]) <= 1 and abs(a[1] - b[1]) <= 1
+    for bad in ([1, -1], [0, 0], [float("nan"), 1]):
+        with pytest.raises(ValueError):
+            kv.shard_range_weighted(10, bad, 0)
+
+
+@pytest.mark.gpu
+def test_weighted_sharded_decode_matches_single_instance():
+    import _oracle as o
+    c = o.codec_by_name("ka9q27")
+    nbytes, n_frames = 16, 257
+    nbits = nbytes * 8
+    T = nbits + c.K - 1
+    syms = np.stack([o.make_frame(c, nbytes, 0.7, seed=6, frame=f)[1] for f in range(n_frames)])
+    ndev = kv.load_library().b200v_device_count()
+    devices = [g % ndev for g in range(3)]
+    weights = [20.4, 35.2, 0.0]                              # a shard may be empty
+    with kv.ShardedDecoder(kv.KA9Q27, T, n_frames, devices, weights=weights) as sd:
+        assert sd.shards() == [kv.shard_range_weighted(n_frames, weights, g) for g in range(3)]
+        assert sd.shards()[2][1] == 0
+        out = sd.decode(syms, nbits)
+    with kv.BatchDecoder(kv.KA9Q27, T, n_frames) as dec:
+        assert np.array_equal(out, dec.decode(syms, nbits))
