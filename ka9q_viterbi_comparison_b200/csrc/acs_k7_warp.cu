@@ -86,6 +86,9 @@ __device__ __forceinline__ void acs_mod_unwrapped(int lo, int hi, int bm, int& s
 #ifndef WARP_MOD_UNWRAPPED
 #define WARP_MOD_UNWRAPPED 1
 #endif
+#ifndef WARP_PACK_SURVIVORS
+#define WARP_PACK_SURVIVORS 0      // K=7: both survivors of a butterfly in one shuffled word (2 shuffles instead of 4 per step): measured no faster for one frame (416 us either way) and slower for 1024 (1.75 vs 1.61 ms); off
+#endif
 
 // RT = code rate known at compile time (2, 3, 4) or 0: run-time c.R (up to MAX_R).
 // Latency matters here as much as throughput -- this is the family a single frame through the reference's
@@ -165,6 +168,11 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
         prepare(nxt, cur);
         fetch(nxt, t0 + 32);
         const int nhere = min(32, a.nsteps - t0);
+        if (UNWRAP && WARP_PACK_SURVIVORS) {      // 16-bit halves: bring the unwrapped values down by a multiple of 256
+            const int ref = __shfl_sync(0xffffffffu, lo, 0);
+            const int sub = ref >= 512 ? ((ref - 256) & ~255) : 0;
+            lo -= sub; hi -= sub;
+        }
         for (int i = 0; i < nhere; i++) {
             uint32_t sw[CW];
 #pragma unroll
@@ -180,10 +188,17 @@ __global__ void __launch_bounds__(128) acs_k7_warp_kernel(const GenericArgs a) {
             if constexpr (UNWRAP) acs_mod_unwrapped(lo, hi, bm, v0, v1, d0, d1);
             else acs<POLICY>(c.max_error, lo, hi, bm, v0, v1, d0, d1);     // new[2j], new[2j+1]
             const unsigned w0 = __ballot_sync(0xffffffffu, d0), w1 = __ballot_sync(0xffffffffu, d1);
-            const int a0 = __shfl_sync(0xffffffffu, v0, src0), a1 = __shfl_sync(0xffffffffu, v1, src0);
-            const int c0 = __shfl_sync(0xffffffffu, v0, src1), c1 = __shfl_sync(0xffffffffu, v1, src1);
-            lo = odd ? a1 : a0;
-            hi = odd ? c1 : c0;
+            if (WARP_PACK_SURVIVORS) {      // both survivors of a butterfly travel as one u16x2 word: two shuffles per step
+                const uint32_t pk = ((uint32_t)v0 & 0xffffu) | ((uint32_t)v1 << 16);
+                const uint32_t pa = __shfl_sync(0xffffffffu, pk, src0), pc = __shfl_sync(0xffffffffu, pk, src1);
+                lo = (int)(odd ? (pa >> 16) : (pa & 0xffffu));
+                hi = (int)(odd ? (pc >> 16) : (pc & 0xffffu));
+            } else {
+                const int a0 = __shfl_sync(0xffffffffu, v0, src0), a1 = __shfl_sync(0xffffffffu, v1, src0);
+                const int c0 = __shfl_sync(0xffffffffu, v0, src1), c1 = __shfl_sync(0xffffffffu, v1, src1);
+                lo = odd ? a1 : a0;
+                hi = odd ? c1 : c0;
+            }
             if (lane == 0) *reinterpret_cast<uint2*>(drow + 2 * (size_t)(t0 + i)) = make_uint2(w0, w1);
             if (PolicyTraits<POLICY>::has_renorm) {
                 const int m0 = __shfl_sync(0xffffffffu, lo, 0);
